@@ -1,0 +1,429 @@
+// api.cu — device scene upload + the hot-path entry points of include/rtw_b200.h.
+// No CPU fallback: every function here fails with RTW_ERR_CUDA when the CUDA runtime or an sm_100 device
+// is missing.
+#include <cmath>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "flat.hpp"
+#include "kernels.hpp"
+
+using namespace rtw;
+
+namespace {
+
+struct DevBuf {
+    void* p = nullptr;
+    template <typename T>
+    cudaError_t upload(const std::vector<T>& v) {
+        if (v.empty()) return cudaSuccess;
+        cudaError_t e = cudaMalloc(&p, v.size() * sizeof(T));
+        if (e != cudaSuccess) return e;
+        return cudaMemcpy(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice);
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+    }
+};
+
+int cuda_fail(cudaError_t e, const char* what) {
+    set_error(std::string(what) + ": " + cudaGetErrorString(e));
+    return RTW_ERR_CUDA;
+}
+
+// Compose a translate/rotate_y chain (outermost first) into local = Ry(o) + t, in FP64.
+void compose_chain(const rtw_flat_scene* fs, int head, DevXf& out) {
+    double C = 1, S = 0, t[3] = {0, 0, 0};
+    for (int i = head; i >= 0; i = fs->xfs[i].next) {
+        const rtw_flat_xf& x = fs->xfs[i];
+        if (x.kind == RTW_XF_TRANSLATE) {  // hittable.h:301: origin - offset
+            t[0] -= x.a, t[1] -= x.b, t[2] -= x.c;
+        } else {  // hittable.h:378-382: x' = cos*x - sin*z, z' = sin*x + cos*z
+            double s = x.a, c = x.b;
+            double nC = c * C - s * S, nS = s * C + c * S;
+            double tx = c * t[0] - s * t[2], tz = s * t[0] + c * t[2];
+            C = nC, S = nS, t[0] = tx, t[2] = tz;
+        }
+    }
+    out = DevXf{(float)C, (float)S, (float)t[0], (float)t[1], (float)t[2], 0, 0, 0};
+}
+
+inline float __int_as_float_host(int v) {
+    float f;
+    memcpy(&f, &v, sizeof f);
+    return f;
+}
+
+int bvh_depth(const rtw_flat_scene* fs, int ref, int depth) {
+    if (ref < 0) return depth;
+    if (depth > 4096) return depth;
+    const rtw_flat_node& n = fs->nodes[ref];
+    int l = bvh_depth(fs, n.left, depth + 1);
+    int r = n.right == n.left ? l : bvh_depth(fs, n.right, depth + 1);
+    return l > r ? l : r;
+}
+
+}  // namespace
+
+struct rtw_scene {
+    int device = 0;
+    DevScene dev{};
+    DevBuf items, pa, pb, pm, pd, xfs, node_lo, node_hi, leaves, mats, texs, texels, ranvec, perm, lights;
+    unsigned long long* d_counter = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    // pending asynchronous render
+    bool pending = false;
+    rtw_render_params pending_params{};
+    int pending_launches = 0;
+    float* scratch_accum = nullptr;  // device buffer behind rtw_render (host API)
+    size_t scratch_pixels = 0;
+    void release() {
+        DevBuf* all[] = {&items, &pa, &pb, &pm, &pd, &xfs, &node_lo, &node_hi, &leaves, &mats, &texs, &texels, &ranvec, &perm, &lights};
+        for (DevBuf* b : all) b->release();
+        if (d_counter) cudaFree(d_counter);
+        if (scratch_accum) cudaFree(scratch_accum);
+        if (ev0) cudaEventDestroy(ev0);
+        if (ev1) cudaEventDestroy(ev1);
+    }
+};
+
+extern "C" int rtw_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    int ok = 0;
+    for (int i = 0; i < n; i++) {
+        cudaDeviceProp p;
+        if (cudaGetDeviceProperties(&p, i) == cudaSuccess && p.major == 10) ok++;
+    }
+    return ok;
+}
+
+// ------------------------------------------------------------------------------------------------ upload
+extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
+    if (!fs || fs->n_world_items < 0) {
+        set_error("scene_create: null flat scene");
+        return nullptr;
+    }
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || device < 0 || device >= ndev) {
+        set_error(std::string("scene_create: no usable CUDA device (") + (e != cudaSuccess ? cudaGetErrorString(e) : "bad index") +
+                  "); this backend has no CPU fallback");
+        cudaGetLastError();
+        return nullptr;
+    }
+    cudaDeviceProp prop;
+    if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess || prop.major != 10) {
+        set_error("scene_create: device is not compute capability 10.x (kernels are built for sm_100a only)");
+        return nullptr;
+    }
+    if ((e = cudaSetDevice(device)) != cudaSuccess) {
+        cuda_fail(e, "cudaSetDevice");
+        return nullptr;
+    }
+    if (fs->n_xfs > (int)PM_XF_MASK - 1 || fs->n_materials >= (1 << 15)) {
+        set_error("scene_create: too many transforms/materials for the packed primitive word");
+        return nullptr;
+    }
+
+    uint32_t feat = 0;
+    std::vector<DevXf> xfs(fs->n_xfs);
+    for (int i = 0; i < fs->n_xfs; i++) compose_chain(fs, i, xfs[i]);  // entry i = chain starting at link i
+    if (fs->n_xfs) feat |= F_XF;
+
+    std::vector<float4> pa(fs->n_prims), pb(fs->n_prims);
+    std::vector<uint32_t> pm(fs->n_prims);
+    std::vector<double> pd;
+    for (int i = 0; i < fs->n_prims; i++) {
+        const rtw_flat_prim& p = fs->prims[i];
+        uint32_t m = (uint32_t)p.type | (p.flip ? PM_FLIP : 0u) | ((uint32_t)(p.xf + 1) << PM_XF_SHIFT) |
+                     ((uint32_t)p.material << PM_MAT_SHIFT);
+        pb[i] = make_float4(0, 0, 0, 0);
+        if (p.type == RTW_PRIM_SPHERE) {
+            pa[i] = make_float4((float)p.v[0], (float)p.v[1], (float)p.v[2], (float)p.v[3]);
+            if (std::fabs(p.v[3]) >= 100.0) {
+                m |= PM_PRECISE;
+                feat |= F_PRECISE;
+                pb[i].w = __int_as_float_host((int)(pd.size() / 4));
+                for (int k = 0; k < 4; k++) pd.push_back(p.v[k]);
+            }
+        } else if (p.type == RTW_PRIM_MOVING_SPHERE) {
+            // sphere.h:22-25: center0 + ((time - time0)/(time1 - time0))*(center1 - center0) = c' + time*delta'
+            double t0 = p.v[7], t1 = p.v[8], inv = 1.0 / (t1 - t0);
+            double d[3], c[3];
+            for (int k = 0; k < 3; k++) {
+                d[k] = (p.v[4 + k] - p.v[k]) * inv;
+                c[k] = p.v[k] - t0 * d[k];
+            }
+            pa[i] = make_float4((float)c[0], (float)c[1], (float)c[2], (float)p.v[3]);
+            pb[i] = make_float4((float)d[0], (float)d[1], (float)d[2], 0.0f);
+            feat |= F_MOVING;
+        } else {
+            pa[i] = make_float4((float)p.v[0], (float)p.v[1], (float)p.v[2], (float)p.v[3]);
+            pb[i].x = (float)p.v[4];
+        }
+        pm[i] = m;
+    }
+
+    std::vector<DevItem> items(fs->n_items);
+    int max_depth = 0;
+    for (int i = 0; i < fs->n_items; i++) {
+        const rtw_flat_item& it = fs->items[i];
+        DevItem d{};
+        d.type = it.type, d.xf = it.xf, d.first = it.first, d.count = it.count;
+        d.material = it.material, d.flip = it.flip;
+        d.density_eff = (float)(it.density * (it.multiplicity > 0 ? it.multiplicity : 1));
+        if (it.type == RTW_ITEM_BVH) {
+            feat |= F_BVH;
+            int dep = bvh_depth(fs, it.first, 0);
+            if (dep > max_depth) max_depth = dep;
+        }
+        if (it.type == RTW_ITEM_MEDIUM) feat |= F_MEDIA;
+        items[i] = d;
+    }
+    if (max_depth > 30) {
+        set_error("scene_create: bvh deeper than the 32-entry traversal stack");
+        return nullptr;
+    }
+
+    std::vector<float4> node_lo(fs->n_nodes), node_hi(fs->n_nodes);
+    for (int i = 0; i < fs->n_nodes; i++) {
+        const rtw_flat_node& n = fs->nodes[i];
+        node_lo[i] = make_float4((float)n.bmin[0], (float)n.bmin[1], (float)n.bmin[2], __int_as_float_host(n.left));
+        node_hi[i] = make_float4((float)n.bmax[0], (float)n.bmax[1], (float)n.bmax[2], __int_as_float_host(n.right));
+    }
+    std::vector<int2> leaves(fs->n_leaves);
+    for (int i = 0; i < fs->n_leaves; i++) leaves[i] = make_int2(fs->leaves[i].first_prim, fs->leaves[i].prim_count);
+
+    std::vector<DevTex> texs(fs->n_textures);
+    for (int i = 0; i < fs->n_textures; i++) {
+        const rtw_flat_texture& t = fs->textures[i];
+        DevTex d{};
+        d.r = (float)t.color[0], d.g = (float)t.color[1], d.b = (float)t.color[2], d.scale = (float)t.scale;
+        d.type = t.type, d.even = t.even, d.odd = t.odd, d.image_offset = t.image_offset, d.nx = t.nx, d.ny = t.ny;
+        texs[i] = d;
+    }
+    std::vector<DevMat> mats(fs->n_materials);
+    for (int i = 0; i < fs->n_materials; i++) {
+        const rtw_flat_material& m = fs->materials[i];
+        DevMat d{};
+        d.type = m.type, d.texture = m.texture;
+        if (m.type == RTW_MAT_METAL) {
+            d.r = (float)m.albedo[0], d.g = (float)m.albedo[1], d.b = (float)m.albedo[2], d.param = (float)m.fuzz;
+            d.tex_is_constant = 1;
+        } else if (m.type == RTW_MAT_DIELECTRIC) {
+            d.param = (float)m.ref_idx;
+            d.tex_is_constant = 1;
+        } else if (m.texture >= 0 && fs->textures[m.texture].type == RTW_TEX_CONSTANT) {
+            const rtw_flat_texture& t = fs->textures[m.texture];
+            d.r = (float)t.color[0], d.g = (float)t.color[1], d.b = (float)t.color[2];
+            d.tex_is_constant = 1;
+        } else {
+            feat |= F_TEXTURES;
+        }
+        mats[i] = d;
+    }
+    std::vector<DevLight> lights(fs->n_lights);
+    for (int i = 0; i < fs->n_lights; i++) {
+        const rtw_flat_light& l = fs->lights[i];
+        DevLight d{};
+        d.type = l.type;
+        d.a0 = (float)l.v[0], d.a1 = (float)l.v[1], d.a2 = (float)l.v[2], d.a3 = (float)l.v[3];
+        if (l.type == RTW_LIGHT_XZ_RECT) {
+            d.k = (float)l.v[4];
+            d.area = (float)((l.v[1] - l.v[0]) * (l.v[3] - l.v[2]));  // hittable.h:217
+        }
+        lights[i] = d;
+    }
+    std::vector<float4> ranvec;
+    std::vector<uint8_t> perm;
+    if (fs->perlin_ranvec) {
+        for (int i = 0; i < 256; i++)
+            ranvec.push_back(make_float4((float)fs->perlin_ranvec[3 * i], (float)fs->perlin_ranvec[3 * i + 1],
+                                         (float)fs->perlin_ranvec[3 * i + 2], 0.0f));
+        for (int i = 0; i < 768; i++) perm.push_back((uint8_t)fs->perlin_perm[i]);
+    }
+    std::vector<uint8_t> texels;
+    if (fs->n_texel_bytes) texels.assign(fs->texels, fs->texels + fs->n_texel_bytes);
+
+    rtw_scene* s = new (std::nothrow) rtw_scene();
+    if (!s) return nullptr;
+    s->device = device;
+    cudaError_t err[] = {s->items.upload(items), s->pa.upload(pa), s->pb.upload(pb), s->pm.upload(pm), s->pd.upload(pd),
+                         s->xfs.upload(xfs), s->node_lo.upload(node_lo), s->node_hi.upload(node_hi), s->leaves.upload(leaves),
+                         s->mats.upload(mats), s->texs.upload(texs), s->texels.upload(texels), s->ranvec.upload(ranvec),
+                         s->perm.upload(perm), s->lights.upload(lights), cudaMalloc(&s->d_counter, sizeof(unsigned long long)),
+                         cudaEventCreate(&s->ev0), cudaEventCreate(&s->ev1)};
+    for (cudaError_t x : err)
+        if (x != cudaSuccess) {
+            cuda_fail(x, "scene upload");
+            s->release();
+            delete s;
+            return nullptr;
+        }
+    DevScene& d = s->dev;
+    d.items = (const DevItem*)s->items.p, d.pa = (const float4*)s->pa.p, d.pb = (const float4*)s->pb.p;
+    d.pm = (const uint32_t*)s->pm.p, d.pd = (const double*)s->pd.p, d.xfs = (const DevXf*)s->xfs.p;
+    d.node_lo = (const float4*)s->node_lo.p, d.node_hi = (const float4*)s->node_hi.p, d.leaves = (const int2*)s->leaves.p;
+    d.mats = (const DevMat*)s->mats.p, d.texs = (const DevTex*)s->texs.p, d.texels = (const uint8_t*)s->texels.p;
+    d.perlin_ranvec = (const float4*)s->ranvec.p, d.perlin_perm = (const uint8_t*)s->perm.p;
+    d.lights = (const DevLight*)s->lights.p;
+    d.n_world_items = fs->n_world_items, d.n_items = fs->n_items, d.n_prims = fs->n_prims, d.n_lights = fs->n_lights;
+    d.render_type = fs->render_type, d.background_type = fs->background_type;
+    d.features = feat, d.max_bvh_depth = max_depth;
+    const rtw_flat_camera& c = fs->camera;
+    DevCamera& k = d.cam;
+    k.ox = (float)c.origin[0], k.oy = (float)c.origin[1], k.oz = (float)c.origin[2];
+    k.llx = (float)c.lower_left_corner[0], k.lly = (float)c.lower_left_corner[1], k.llz = (float)c.lower_left_corner[2];
+    k.hx = (float)c.horizontal[0], k.hy = (float)c.horizontal[1], k.hz = (float)c.horizontal[2];
+    k.vx = (float)c.vertical[0], k.vy = (float)c.vertical[1], k.vz = (float)c.vertical[2];
+    k.ux = (float)c.u[0], k.uy = (float)c.u[1], k.uz = (float)c.u[2];
+    k.wx = (float)c.v[0], k.wy = (float)c.v[1], k.wz = (float)c.v[2];
+    k.time0 = (float)c.time0, k.time1 = (float)c.time1, k.lens_radius = (float)c.lens_radius;
+    return s;
+}
+
+extern "C" void rtw_scene_destroy(rtw_scene* s) {
+    if (!s) return;
+    cudaSetDevice(s->device);
+    s->release();
+    delete s;
+}
+
+// ------------------------------------------------------------------------------------------------ hot path
+namespace {
+
+int check_params(const rtw_scene* s, const rtw_render_params* p) {
+    if (!s || !p) {
+        set_error("render: null scene or params");
+        return RTW_ERR_INVALID;
+    }
+    if (p->nx <= 0 || p->ny <= 0 || p->spp_count <= 0 || p->spp_begin < 0 || p->max_depth < 0 ||
+        (long long)p->nx * p->ny > 0x7fffffffLL) {
+        set_error("render: bad nx/ny/spp/max_depth");
+        return RTW_ERR_INVALID;
+    }
+    return RTW_OK;
+}
+
+}  // namespace
+
+extern "C" int rtw_render_device(rtw_scene* s, const rtw_render_params* p, float* accum_dev, void* cuda_stream) {
+    int rc = check_params(s, p);
+    if (rc != RTW_OK) return rc;
+    if (!accum_dev) {
+        set_error("render: null accumulator");
+        return RTW_ERR_INVALID;
+    }
+    if (p->flags & RTW_FLAG_WAVEFRONT) {
+        set_error("render: wavefront pipeline not built in this round");
+        return RTW_ERR_UNSUPPORTED;
+    }
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    cudaError_t e = cudaSetDevice(s->device);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
+    DevRenderParams rp{};
+    rp.nx = p->nx, rp.ny = p->ny, rp.spp_begin = p->spp_begin, rp.spp_count = p->spp_count, rp.max_depth = p->max_depth;
+    rp.flags = p->flags;
+    rp.seed_lo = (uint32_t)(p->seed & 0xffffffffu), rp.seed_hi = (uint32_t)(p->seed >> 32);
+    if ((e = cudaMemsetAsync(s->d_counter, 0, sizeof(unsigned long long), st)) != cudaSuccess) return cuda_fail(e, "memset");
+    if ((e = cudaEventRecord(s->ev0, st)) != cudaSuccess) return cuda_fail(e, "event");
+    if ((e = launch_render(s->dev, rp, (float4*)accum_dev, s->d_counter, st)) != cudaSuccess) return cuda_fail(e, "render launch");
+    if ((e = cudaEventRecord(s->ev1, st)) != cudaSuccess) return cuda_fail(e, "event");
+    s->pending = true;
+    s->pending_params = *p;
+    s->pending_launches = 1;
+    return RTW_OK;
+}
+
+extern "C" int rtw_render_device_finish(rtw_scene* s, rtw_render_stats* stats) {
+    if (!s || !s->pending) {
+        set_error("render_device_finish: no pending render");
+        return RTW_ERR_INVALID;
+    }
+    cudaError_t e = cudaSetDevice(s->device);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
+    if ((e = cudaEventSynchronize(s->ev1)) != cudaSuccess) return cuda_fail(e, "render kernel");
+    s->pending = false;
+    if (stats) {
+        unsigned long long rays = 0;
+        if ((e = cudaMemcpy(&rays, s->d_counter, sizeof rays, cudaMemcpyDeviceToHost)) != cudaSuccess) return cuda_fail(e, "counter");
+        float ms = 0;
+        cudaEventElapsedTime(&ms, s->ev0, s->ev1);
+        const rtw_render_params& p = s->pending_params;
+        stats->paths = (uint64_t)p.nx * p.ny * p.spp_count;
+        stats->rays = rays;
+        stats->kernel_ms = ms;
+        stats->kernel_launches = s->pending_launches;
+        stats->pad_ = 0;
+    }
+    return RTW_OK;
+}
+
+extern "C" int rtw_render(rtw_scene* s, const rtw_render_params* p, float* accum_host, rtw_render_stats* stats) {
+    int rc = check_params(s, p);
+    if (rc != RTW_OK) return rc;
+    if (!accum_host) {
+        set_error("render: null accumulator");
+        return RTW_ERR_INVALID;
+    }
+    cudaError_t e = cudaSetDevice(s->device);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
+    size_t pixels = (size_t)p->nx * p->ny;
+    if (pixels > s->scratch_pixels) {
+        if (s->scratch_accum) cudaFree(s->scratch_accum);
+        s->scratch_accum = nullptr;
+        s->scratch_pixels = 0;
+        if ((e = cudaMalloc(&s->scratch_accum, pixels * 4 * sizeof(float))) != cudaSuccess) return cuda_fail(e, "cudaMalloc accum");
+        s->scratch_pixels = pixels;
+    }
+    if (p->flags & RTW_FLAG_ACCUMULATE)
+        if ((e = cudaMemcpy(s->scratch_accum, accum_host, pixels * 16, cudaMemcpyHostToDevice)) != cudaSuccess) return cuda_fail(e, "H2D accum");
+    rc = rtw_render_device(s, p, s->scratch_accum, nullptr);
+    if (rc != RTW_OK) return rc;
+    rc = rtw_render_device_finish(s, stats);
+    if (rc != RTW_OK) return rc;
+    if ((e = cudaMemcpy(accum_host, s->scratch_accum, pixels * 16, cudaMemcpyDeviceToHost)) != cudaSuccess) return cuda_fail(e, "D2H accum");
+    return RTW_OK;
+}
+
+extern "C" int rtw_intersect_batch_device(rtw_scene* s, const rtw_ray* rays, rtw_hit* hits, int64_t n, float tmin, float tmax,
+                                          void* cuda_stream) {
+    if (!s || n < 0 || (n > 0 && (!rays || !hits))) {
+        set_error("intersect_batch: bad arguments");
+        return RTW_ERR_INVALID;
+    }
+    if (n == 0) return RTW_OK;
+    cudaError_t e = cudaSetDevice(s->device);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
+    if ((e = launch_intersect(s->dev, rays, hits, n, tmin, tmax, (cudaStream_t)cuda_stream)) != cudaSuccess)
+        return cuda_fail(e, "intersect launch");
+    return RTW_OK;
+}
+
+extern "C" int rtw_intersect_batch(rtw_scene* s, const rtw_ray* rays, rtw_hit* hits, int64_t n, float tmin, float tmax) {
+    if (!s || n < 0 || (n > 0 && (!rays || !hits))) {
+        set_error("intersect_batch: bad arguments");
+        return RTW_ERR_INVALID;
+    }
+    if (n == 0) return RTW_OK;
+    cudaError_t e = cudaSetDevice(s->device);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
+    rtw_ray* d_rays = nullptr;
+    rtw_hit* d_hits = nullptr;
+    int rc = RTW_OK;
+    if ((e = cudaMalloc(&d_rays, n * sizeof(rtw_ray))) != cudaSuccess || (e = cudaMalloc(&d_hits, n * sizeof(rtw_hit))) != cudaSuccess ||
+        (e = cudaMemcpy(d_rays, rays, n * sizeof(rtw_ray), cudaMemcpyHostToDevice)) != cudaSuccess) {
+        rc = cuda_fail(e, "intersect_batch buffers");
+    } else if ((rc = rtw_intersect_batch_device(s, d_rays, d_hits, n, tmin, tmax, nullptr)) == RTW_OK) {
+        if ((e = cudaMemcpy(hits, d_hits, n * sizeof(rtw_hit), cudaMemcpyDeviceToHost)) != cudaSuccess) rc = cuda_fail(e, "intersect_batch D2H");
+    }
+    if (d_rays) cudaFree(d_rays);
+    if (d_hits) cudaFree(d_hits);
+    return rc;
+}

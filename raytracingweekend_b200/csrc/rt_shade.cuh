@@ -1,0 +1,213 @@
+// rt_shade.cuh — textures, sampling utilities, pdfs, materials, camera, background (FP32 device forms).
+#pragma once
+#include "rt_trace.cuh"
+
+namespace rtw {
+
+constexpr float kPi = 3.14159265358979323846f;
+
+// ------------------------------------------------------------------------------------------------ Perlin
+// perlin::noise (noise.h:89-151, InterpolationType::PERLIN) + perlin_interp (noise.h:40-60) with the Hermite
+// cubic `smooth` (noise.h:9-12, :19).
+RTW_DEV float perlin_noise(const DevScene& sc, V3 p) {
+    float fx = floorf(p.x), fy = floorf(p.y), fz = floorf(p.z);
+    float u = p.x - fx, v = p.y - fy, w = p.z - fz;
+    int i = (int)fx, j = (int)fy, k = (int)fz;
+    float uu = u * u * (3.0f - 2.0f * u), vv = v * v * (3.0f - 2.0f * v), ww = w * w * (3.0f - 2.0f * w);
+    const uint8_t* px = sc.perlin_perm;
+    const uint8_t* py = sc.perlin_perm + 256;
+    const uint8_t* pz = sc.perlin_perm + 512;
+    float accum = 0.0f;
+#pragma unroll
+    for (int di = 0; di < 2; di++) {
+        int hx = __ldg(&px[(i + di) & 255]);
+        float wi = di ? uu : 1.0f - uu;
+#pragma unroll
+        for (int dj = 0; dj < 2; dj++) {
+            int hy = __ldg(&py[(j + dj) & 255]);
+            float wj = dj ? vv : 1.0f - vv;
+#pragma unroll
+            for (int dk = 0; dk < 2; dk++) {
+                int hz = __ldg(&pz[(k + dk) & 255]);
+                float wk = dk ? ww : 1.0f - ww;
+                float4 c = ldg4(&sc.perlin_ranvec[hx ^ hy ^ hz]);
+                float dp = fmaf(c.x, u - di, fmaf(c.y, v - dj, c.z * (w - dk)));
+                accum = fmaf(wi * wj * wk, dp, accum);
+            }
+        }
+    }
+    return accum;
+}
+RTW_DEV float perlin_turb(const DevScene& sc, V3 p) {  // noise.h:74-86, depth 7
+    float accum = 0.0f, weight = 1.0f;
+    for (int i = 0; i < 7; i++) {
+        accum = fmaf(weight, perlin_noise(sc, p), accum);
+        weight *= 0.5f;
+        p = p * 2.0f;
+    }
+    return fabsf(accum);
+}
+
+// texture::value(u, v, p) (texture.h:21-24, 35-46, 57-68, 81-94)
+RTW_DEV V3 texture_value(const DevScene& sc, int tex, float u, float v, V3 p) {
+    for (int guard = 0; guard < 16; guard++) {
+        DevTex t = sc.texs[tex];
+        if (t.type == RTW_TEX_CONSTANT) return mk(t.r, t.g, t.b);
+        if (t.type == RTW_TEX_CHECKER) {
+            float sines = sinf(10.0f * p.x) * sinf(10.0f * p.y) * sinf(10.0f * p.z);
+            tex = (sines < 0.0f) ? t.odd : t.even;
+            continue;
+        }
+        if (t.type == RTW_TEX_NOISE) {
+            float g = 0.5f * (1.0f + sinf(fmaf(t.scale, p.z, 10.0f * perlin_turb(sc, p))));
+            return mk(g, g, g);
+        }
+        // image_texture (texture.h:81-94): nearest texel, v flipped
+        int i = (int)(u * t.nx);
+        int j = (int)((1.0f - v) * t.ny - 0.001f);
+        i = max(min(i, t.nx - 1), 0);
+        j = max(min(j, t.ny - 1), 0);
+        const uint8_t* px = sc.texels + t.image_offset + 3 * i + 3 * t.nx * j;
+        return mk(__ldg(px) / 255.0f, __ldg(px + 1) / 255.0f, __ldg(px + 2) / 255.0f);
+    }
+    return mk(0.0f, 0.0f, 0.0f);
+}
+
+RTW_DEV V3 material_texture(const DevScene& sc, const DevMat& m, float u, float v, V3 p) {
+    if (m.tex_is_constant) return mk(m.r, m.g, m.b);
+    return texture_value(sc, m.texture, u, v, p);
+}
+
+// ------------------------------------------------------------------------------------------------ sampling
+struct Onb {  // onb.h:32-38
+    V3 u, v, w;
+};
+RTW_DEV Onb onb_from_w(V3 n) {
+    Onb b;
+    b.w = normalize(n);
+    V3 a = (fabsf(b.w.x) > 0.9f) ? mk(0.0f, 1.0f, 0.0f) : mk(1.0f, 0.0f, 0.0f);
+    b.v = normalize(cross(b.w, a));
+    b.u = cross(b.w, b.v);
+    return b;
+}
+RTW_DEV V3 onb_local(const Onb& b, V3 a) { return a.x * b.u + a.y * b.v + a.z * b.w; }  // onb.h:21-24
+
+RTW_DEV V3 random_cosine_direction(float r1, float r2) {  // utility.h:54-67
+    float z = sqrtf(1.0f - r2);
+    float s, c;
+    sincospif(2.0f * r1, &s, &c);
+    float sr = sqrtf(r2);
+    return mk(c * sr, s * sr, z);
+}
+// utility.h:69-82. 1 - cos_theta_max is formed as q/(1+sqrt(1-q)) (no cancellation for far spheres).
+RTW_DEV V3 random_to_sphere(float radius, float distance_squared, float r1, float r2) {
+    float q = radius * radius / distance_squared;
+    float one_minus_cmax = q / (1.0f + sqrtf(1.0f - q));
+    float omz = r2 * one_minus_cmax;
+    float z = 1.0f - omz;
+    float st = sqrtf(omz * (1.0f + z));  // sqrt(1 - z*z)
+    float s, c;
+    sincospif(2.0f * r1, &s, &c);
+    return mk(c * st, s * st, z);
+}
+// random_in_unit_sphere (utility.h:27-35) without the rejection loop: uniform direction * cbrt(U) is the same
+// distribution (uniform in the unit ball).
+RTW_DEV V3 random_in_unit_ball(float u0, float u1, float u2) {
+    float z = 1.0f - 2.0f * u0;
+    float r = sqrtf(fmaxf(0.0f, 1.0f - z * z));
+    float s, c;
+    sincospif(2.0f * u1, &s, &c);
+    float rad = cbrtf(u2);
+    return mk(rad * r * c, rad * r * s, rad * z);
+}
+
+// ------------------------------------------------------------------------------------------------ light pdfs
+// xz_rect::pdf_value (hittable.h:208-222): self-hit test with t in [0.001, +inf], no occlusion.
+RTW_DEV float light_rect_pdf(const DevLight& l, V3 o, V3 v) {
+    float t = __fdiv_rn(l.k - o.y, v.y);
+    if (t < 0.001f || t > INFINITY) return 0.0f;
+    float x = fmaf(t, v.x, o.x), z = fmaf(t, v.z, o.z);
+    if (x < l.a0 || x > l.a1 || z < l.a2 || z > l.a3) return 0.0f;
+    float len2 = dot(v, v);
+    float distance_squared = t * t * len2;
+    float cosine = fabsf(v.y * rsqrtf(len2));
+    return distance_squared / (cosine * l.area);
+}
+// sphere_base::pdf_value (sphere.h:88-99)
+RTW_DEV float light_sphere_pdf(const DevLight& l, V3 o, V3 v) {
+    V3 c = mk(l.a0, l.a1, l.a2);
+    float t0, t1, t;
+    if (!sphere_roots(o - c, v, l.a3, t0, t1) || !sphere_pick(t0, t1, 0.001f, INFINITY, t)) return 0.0f;
+    V3 co = c - o;
+    float q = l.a3 * l.a3 / dot(co, co);
+    float one_minus_cmax = q / (1.0f + sqrtf(1.0f - q));  // NaN when the origin is inside, like the reference (Q17)
+    return 1.0f / (2.0f * kPi * one_minus_cmax);
+}
+// hittable_list::pdf_value (hittable_list.h:44-53)
+RTW_DEV float lights_pdf(const DevScene& sc, V3 o, V3 v) {
+    float weight = 1.0f / (float)sc.n_lights;
+    float sum = 0.0f;
+    for (int i = 0; i < sc.n_lights; i++) {
+        DevLight l = sc.lights[i];
+        float pv = 0.0f;  // hittable.h:36 default
+        if (l.type == RTW_LIGHT_XZ_RECT) pv = light_rect_pdf(l, o, v);
+        else if (l.type == RTW_LIGHT_SPHERE) pv = light_sphere_pdf(l, o, v);
+        sum = fmaf(weight, pv, sum);
+    }
+    return sum;
+}
+// hittable_list::random (hittable_list.h:55-59) -> xz_rect::random (hittable.h:224-228) |
+// sphere_base::random (sphere.h:101-108) | hittable::random default (hittable.h:37)
+RTW_DEV V3 lights_random(const DevScene& sc, V3 o, float upick, float r1, float r2) {
+    int n = sc.n_lights;
+    int idx = min(n - 1, (int)((float)n * upick));  // utility.h:22-25 with a = 0, b = n-1
+    DevLight l = sc.lights[idx];
+    if (l.type == RTW_LIGHT_XZ_RECT) {
+        V3 pt = mk(fmaf(l.a1 - l.a0, r1, l.a0), l.k, fmaf(l.a3 - l.a2, r2, l.a2));
+        return pt - o;
+    }
+    if (l.type == RTW_LIGHT_SPHERE) {
+        V3 dir = mk(l.a0, l.a1, l.a2) - o;
+        Onb uvw = onb_from_w(dir);
+        return onb_local(uvw, random_to_sphere(l.a3, dot(dir, dir), r1, r2));
+    }
+    return mk(1.0f, 0.0f, 0.0f);
+}
+
+// ------------------------------------------------------------------------------------------------ camera
+// RayTracingWeekend.cpp:227-231 + camera::get_ray (camera.h:36-50).  The lens disk is sampled directly
+// (sqrt(u), 2*pi*v) instead of by rejection (camera.h:61-69) — same distribution — and skipped when aperture = 0.
+RTW_DEV Ray camera_ray(const DevScene& sc, const DevRenderParams& rp, const Rng& rng, int i, int j) {
+    const DevCamera& c = sc.cam;
+    U4 r = rng.draw(0, SITE_MAIN);
+    float s = ((float)i + r.x) / (float)rp.nx;
+    float t = ((float)j + r.y) / (float)rp.ny;
+    V3 origin = mk(c.ox, c.oy, c.oz);
+    V3 offset = mk(0.0f, 0.0f, 0.0f);
+    if (c.lens_radius > 0.0f) {
+        U4 q = rng.draw(0, SITE_LENS);
+        float rad = c.lens_radius * sqrtf(q.x);
+        float sn, cs;
+        sincospif(2.0f * q.y, &sn, &cs);
+        offset = (rad * cs) * mk(c.ux, c.uy, c.uz) + (rad * sn) * mk(c.wx, c.wy, c.wz);
+    }
+    Ray ray;
+    ray.time = fmaf(r.z, c.time1 - c.time0, c.time0);
+    V3 dir = mk(c.llx, c.lly, c.llz) + s * mk(c.hx, c.hy, c.hz) + t * mk(c.vx, c.vy, c.vz) - origin - offset;
+    ray.o = origin + offset;
+    ray.d = normalize(dir);
+    return ray;
+}
+
+// RayTracingWeekend.cpp:143-158
+RTW_DEV V3 background(const DevScene& sc, V3 d) {
+    if (sc.background_type == RTW_BG_GRADIENT) {
+        V3 unit = normalize(d);
+        float t = 0.5f * (unit.y + 1.0f);
+        // lerp(from, to, t) = (1-t)*to + t*from (vec3.h:84-87): white at t = 0, (0.5, 0.7, 1) at t = 1
+        return (1.0f - t) * mk(1.0f, 1.0f, 1.0f) + t * mk(0.5f, 0.7f, 1.0f);
+    }
+    return mk(0.0f, 0.0f, 0.0f);
+}
+
+}  // namespace rtw
