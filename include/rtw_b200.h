@@ -318,6 +318,8 @@ int rtw_tonemap(const float* accum_rgba, int nx, int ny, double* canvas_rgb);
 /* RayTracingWeekend.cpp:252-275: "P3", top row first, int(255.99f*c), one pixel per line. */
 int rtw_write_ppm(const char* path, const double* canvas_rgb, int nx, int ny);
 
+/* Measured FP32 FFMA throughput of `device` in TFLOP/s (roofline denominator). */
+int rtw_measure_fp32_peak(int device, double* tflops);
 /* Device utility: number of CUDA devices with compute capability 10.x (0 = none / no driver). */
 int rtw_device_count(void);
 

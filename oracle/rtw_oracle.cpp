@@ -103,12 +103,35 @@ struct Rec {  // hittable.h:16-29 + ids
 };
 
 
+// ------------------------------------------------------------------------------------------------ event counts
+// Algorithmic-work accounting for the roofline: every event of the reference's math is
+// counted once per occurrence on a SINGLE list pass (the second pass of hittable_list::hit repeats work without
+// changing the result) and with one self-hit test per light pdf evaluation folded into that pdf's cost.
+enum Ev {
+    EV_CAMERA, EV_LENS, EV_RECT_TEST, EV_RECT_ACCEPT, EV_SPHERE_TEST, EV_SPHERE_ROOT, EV_SPHERE_ACCEPT, EV_MOVING_CENTER,
+    EV_AABB, EV_TRANSLATE, EV_ROTATE, EV_FLIP, EV_MEDIUM, EV_BACKGROUND, EV_EMITTED, EV_ONB, EV_COSINE_GEN, EV_COSINE_VALUE,
+    EV_SCATTERING_PDF, EV_LIGHT_PICK, EV_RECT_RANDOM, EV_RECT_PDF, EV_SPHERE_RANDOM, EV_SPHERE_PDF, EV_MIXTURE, EV_LAMBERT_UPDATE,
+    EV_SPECULAR_UPDATE, EV_METAL, EV_DIELECTRIC, EV_ISOTROPIC, EV_CHECKER, EV_IMAGE_TEX, EV_PERLIN_NOISE, EV_NOISE_TEX, EV_RAY,
+    EV_COUNT
+};
+thread_local uint64_t* g_ev = nullptr;  // null = counting off (also while inside a light pdf's self-hit test)
+inline void ev(int e, uint64_t n = 1) {
+    if (g_ev) g_ev[e] += n;
+}
+struct EvSuspend {
+    uint64_t* saved;
+    EvSuspend() : saved(g_ev) { g_ev = nullptr; }
+    ~EvSuspend() { g_ev = saved; }
+};
+
 // sphere_base::hit (sphere.h:46-81)
 bool sphere_hit(const rtw_flat_prim& s, const Ray& r, double t_min, double t_max, Rec& rec) {
     V center = mk(s.v[0], s.v[1], s.v[2]);
     double radius = s.v[3];
     V cur = center;
+    ev(EV_SPHERE_TEST);
     if (s.type == RTW_PRIM_MOVING_SPHERE) {  // sphere.h:22-25
+        ev(EV_MOVING_CENTER);
         V c1 = mk(s.v[4], s.v[5], s.v[6]);
         cur = center + ((r.time - s.v[7]) / (s.v[8] - s.v[7])) * (c1 - center);
     }
@@ -120,7 +143,9 @@ bool sphere_hit(const rtw_flat_prim& s, const Ray& r, double t_min, double t_max
     if (discriminant > 0) {
         double temp = (-b - std::sqrt(discriminant)) / a;
         for (int root = 0; root < 2; root++) {
+            ev(EV_SPHERE_ROOT);
             if (temp < t_max && temp > t_min) {
+                ev(EV_SPHERE_ACCEPT);
                 rec.t = temp;
                 rec.p = r.at(rec.t);
                 rec.normal = (rec.p - cur) / radius;
@@ -144,11 +169,13 @@ bool rect_hit(const rtw_flat_prim& q, const Ray& r, double t0, double t1, Rec& r
     else if (q.type == RTW_PRIM_XZ_RECT) n = 1, a = 0, b = 2;
     else n = 0, a = 1, b = 2;
     double k = q.v[4];
+    ev(EV_RECT_TEST);
     double t = (k - comp(r.o, n)) / comp(r.d, n);
     if (t < t0 || t > t1) return false;
     double ca = comp(r.o, a) + t * comp(r.d, a);
     double cb = comp(r.o, b) + t * comp(r.d, b);
     if (ca < q.v[0] || ca > q.v[1] || cb < q.v[2] || cb > q.v[3]) return false;
+    ev(EV_RECT_ACCEPT);
     rec.u = (ca - q.v[0]) / (q.v[1] - q.v[0]);
     rec.v = (cb - q.v[2]) / (q.v[3] - q.v[2]);
     rec.t = t;
@@ -160,6 +187,7 @@ bool rect_hit(const rtw_flat_prim& q, const Ray& r, double t0, double t1, Rec& r
 
 // aabb::hit (aabb.h:17-47)
 bool aabb_hit(const double* mn, const double* mx, const Ray& r, double tmin, double tmax) {
+    ev(EV_AABB);
     for (int axis = 0; axis < 3; axis++) {
         double invD = 1.0 / comp(r.d, axis);
         double t0 = (mn[axis] - comp(r.o, axis)) * invD;
@@ -177,6 +205,7 @@ bool aabb_hit(const double* mn, const double* mx, const Ray& r, double tmin, dou
 bool prim_hit(const rtw_flat_scene* fs, int pi, int chain, const Ray& r, double t_min, double t_max, Rec& rec) {
     if (chain >= 0) {
         const rtw_flat_xf& x = fs->xfs[chain];
+        ev(x.kind == RTW_XF_TRANSLATE ? EV_TRANSLATE : EV_ROTATE);
         if (x.kind == RTW_XF_TRANSLATE) {
             V off = mk(x.a, x.b, x.c);
             Ray moved{r.o - off, r.d, r.time};
@@ -209,7 +238,10 @@ bool prim_hit(const rtw_flat_scene* fs, int pi, int chain, const Ray& r, double 
     bool h = q.type <= RTW_PRIM_MOVING_SPHERE ? sphere_hit(q, r, t_min, t_max, rec) : rect_hit(q, r, t_min, t_max, rec);
     if (h) {
         rec.prim = pi;
-        if (q.flip) rec.normal = -rec.normal;
+        if (q.flip) {
+            ev(EV_FLIP);
+            rec.normal = -rec.normal;
+        }
     }
     return h;
 }
@@ -230,13 +262,17 @@ bool prims_list_hit(const rtw_flat_scene* fs, int first, int count, const Ray& r
     Rec temp;
     bool hit_anything = false;
     double closest = t_max;
-    for (int pass = 0; pass < 2; pass++)
+    uint64_t* saved = g_ev;
+    for (int pass = 0; pass < 2; pass++) {
+        if (pass == 1) g_ev = nullptr;  // the second pass repeats the first (event accounting: single pass)
         for (int i = first; i < first + count; i++)
             if (prim_hit(fs, i, fs->prims[i].xf, r, t_min, closest, temp)) {
                 hit_anything = true;
                 closest = temp.t;
                 rec = temp;
             }
+    }
+    g_ev = saved;
     return hit_anything;
 }
 
@@ -273,6 +309,7 @@ template <typename Inner>
 bool with_chain(const rtw_flat_scene* fs, int chain, const Ray& r, Rec& rec, Inner inner) {
     if (chain < 0) return inner(r, rec);
     const rtw_flat_xf& x = fs->xfs[chain];
+    ev(x.kind == RTW_XF_TRANSLATE ? EV_TRANSLATE : EV_ROTATE);
     if (x.kind == RTW_XF_TRANSLATE) {
         V off = mk(x.a, x.b, x.c);
         Ray moved{r.o - off, r.d, r.time};
@@ -318,6 +355,7 @@ bool medium_hit(const World& w, int item_index, int medium_index, const Ray& r0,
                 if (rec2.t > t_max) rec2.t = t_max;
                 if (rec1.t >= rec2.t) return false;
                 if (rec1.t < 0) rec1.t = 0;
+                ev(EV_MEDIUM);
                 double distance_inside_boundary = (rec2.t - rec1.t) * length(r.d);
                 double hit_distance;
                 if (w.rng->mode == MODE_MINSTD) {
@@ -349,17 +387,30 @@ bool world_hit(const World& w, const Ray& r, double t_min, double t_max, Rec& re
     bool hit_anything = false;
     double closest = t_max;
     int passes = 2;
+    uint64_t* saved_ev = g_ev;
     for (int pass = 0; pass < passes; pass++) {
+        if (pass == 1) g_ev = nullptr;
         int medium_index = 0;
+        int prev_xf = -1;
         for (int ii = 0; ii < fs->n_world_items; ii++) {
             const rtw_flat_item& it = fs->items[ii];
             if (it.type == RTW_ITEM_PRIMS) {
-                for (int i = it.first; i < it.first + it.count; i++)
-                    if (prim_hit(fs, i, fs->prims[i].xf, r, t_min, closest, temp)) {
+                for (int i = it.first; i < it.first + it.count; i++) {
+                    // a wrapped object (e.g. translate(rotate_y(box))) transforms the ray once for all its rects
+                    int xf = fs->prims[i].xf;
+                    if (xf != prev_xf && xf >= 0)
+                        for (int l = xf; l >= 0; l = fs->xfs[l].next) ev(fs->xfs[l].kind == RTW_XF_TRANSLATE ? EV_TRANSLATE : EV_ROTATE);
+                    prev_xf = xf;
+                    uint64_t* keep = g_ev;
+                    uint64_t tr0 = keep ? keep[EV_TRANSLATE] : 0, ro0 = keep ? keep[EV_ROTATE] : 0;
+                    bool h = prim_hit(fs, i, xf, r, t_min, closest, temp);
+                    if (keep) keep[EV_TRANSLATE] = tr0, keep[EV_ROTATE] = ro0;  // per-primitive chain walks are not reference work
+                    if (h) {
                         hit_anything = true;
                         closest = temp.t;
                         rec = temp;
                     }
+                }
             } else if (it.type == RTW_ITEM_BVH) {
                 bool h = with_chain(fs, it.xf, r, temp, [&](const Ray& rl, Rec& q) { return bvh_hit(fs, it.first, rl, t_min, closest, q); });
                 if (h) {
@@ -381,6 +432,9 @@ bool world_hit(const World& w, const Ray& r, double t_min, double t_max, Rec& re
             }
         }
     }
+    g_ev = saved_ev;
+    if (hit_anything && rec.prim >= 0 && fs->prims[rec.prim].xf >= 0)  // p / normal transformed back once for the winner
+        for (int l = fs->prims[rec.prim].xf; l >= 0; l = fs->xfs[l].next) ev(fs->xfs[l].kind == RTW_XF_TRANSLATE ? EV_TRANSLATE : EV_ROTATE);
     return hit_anything;
 }
 
@@ -391,6 +445,7 @@ namespace {
 // ------------------------------------------------------------------------------------------------ textures
 // perlin::noise / perlin_interp / turb (noise.h:40-60, 74-86, 89-151), Hermite-cubic smoothing (noise.h:9-12,19)
 double perlin_noise(const rtw_flat_scene* fs, V p) {
+    ev(EV_PERLIN_NOISE);
     double u = p.x - floor(p.x), v = p.y - floor(p.y), w = p.z - floor(p.z);
     int i = (int)floor(p.x), j = (int)floor(p.y), k = (int)floor(p.z);
     const int32_t *px = fs->perlin_perm, *py = fs->perlin_perm + 256, *pz = fs->perlin_perm + 512;
@@ -429,11 +484,15 @@ V texture_value(const rtw_flat_scene* fs, int ti, double u, double v, V p) {
     switch (t.type) {
         case RTW_TEX_CONSTANT: return mk(t.color[0], t.color[1], t.color[2]);
         case RTW_TEX_CHECKER: {
+            ev(EV_CHECKER);
             double sines = std::sin(10.0 * p.x) * std::sin(10.0 * p.y) * std::sin(10.0 * p.z);
             return texture_value(fs, sines < 0 ? t.odd : t.even, u, v, p);
         }
-        case RTW_TEX_NOISE: return mk(1, 1, 1) * 0.5f * (1 + sin(t.scale * p.z + 10 * perlin_turb(fs, p)));
+        case RTW_TEX_NOISE:
+            ev(EV_NOISE_TEX);
+            return mk(1, 1, 1) * 0.5f * (1 + sin(t.scale * p.z + 10 * perlin_turb(fs, p)));
         default: {
+            ev(EV_IMAGE_TEX);
             int i = (int)(u * t.nx);
             int j = (int)((1 - v) * t.ny - 0.001f);
             i = std::max(std::min(i, t.nx - 1), 0);
@@ -453,6 +512,7 @@ struct Onb {  // onb.h
     V local(V a) const { return a.x * u + a.y * v + a.z * w; }  // onb.h:21-24
 };
 Onb onb_from_w(V n) {  // onb.h:32-38
+    ev(EV_ONB);
     Onb b;
     b.w = normalize(n);
     V a = (fabs(b.w.x) > 0.9) ? mk(0, 1, 0) : mk(1, 0, 0);
@@ -501,6 +561,8 @@ rtw_flat_prim light_as_prim(const rtw_flat_light& l) {
     return q;
 }
 double light_pdf_value(const rtw_flat_light& l, V o, V v) {
+    ev(l.type == RTW_LIGHT_XZ_RECT ? EV_RECT_PDF : (l.type == RTW_LIGHT_SPHERE ? EV_SPHERE_PDF : EV_COUNT - 1), l.type ? 1 : 0);
+    EvSuspend quiet;  // the pdf's own hit test is part of its cost (Appendix D)
     Rec rec;
     Ray r{o, v, (double)FLT_MAX};
     if (l.type == RTW_LIGHT_XZ_RECT) {  // hittable.h:208-222
@@ -527,6 +589,10 @@ double lights_pdf_value(const rtw_flat_scene* fs, V o, V v) {  // hittable_list.
     return sum;
 }
 V light_random(const rtw_flat_light& l, V o, double r1, double r2) {
+    ev(EV_LIGHT_PICK);
+    if (l.type == RTW_LIGHT_XZ_RECT) ev(EV_RECT_RANDOM);
+    if (l.type == RTW_LIGHT_SPHERE) ev(EV_SPHERE_RANDOM);
+    EvSuspend quiet;  // ONB build is inside the sphere-random cost
     if (l.type == RTW_LIGHT_XZ_RECT) {  // hittable.h:224-228 (r1 -> x, r2 -> z)
         V random = mk(l.v[0] + (l.v[1] - l.v[0]) * r1, l.v[4], l.v[2] + (l.v[3] - l.v[2]) * r2);
         return random - o;
@@ -599,6 +665,7 @@ struct Tracer {
 
     V background(const Ray& r) {  // RayTracingWeekend.cpp:143-158
         if (fs->background_type == RTW_BG_GRADIENT) {
+            ev(EV_BACKGROUND);
             V unit_direction = normalize(r.d);
             double t = 0.5f * (unit_direction.y + 1.0);
             V from = mk(0.5f, 0.7f, 1.0), to = mk(1.0, 1.0, 1.0);
@@ -611,6 +678,7 @@ struct Tracer {
     V color(const Ray& r, int depth, uint32_t bounce) {
         if (depth <= 0) return mk(0, 0, 0);
         rays++;
+        ev(EV_RAY);
         Rec rec;
         World w{fs, &rng, bounce};
         if (!world_hit(w, r, 0.001f, std::numeric_limits<double>::max(), rec)) return background(r);
@@ -618,9 +686,11 @@ struct Tracer {
         const rtw_flat_material& m = fs->materials[rec.mat];
         switch (m.type) {
             case RTW_MAT_DIFFUSE_LIGHT:  // material.h:232-244: emitted one-sided, no scatter (:62-63)
+                ev(EV_EMITTED);
                 if (dot(rec.normal, r.d) > 0) return texture_value(fs, m.texture, rec.u, rec.v, rec.p);
                 return mk(0, 0, 0);
             case RTW_MAT_METAL: {  // material.h:128-136, then :114-115
+                ev(EV_METAL), ev(EV_SPECULAR_UPDATE);
                 V reflected = reflect(normalize(r.d), rec.normal);
                 V dir;
                 if (rng.mode == MODE_PHILOX && m.fuzz == 0.0) dir = reflected;  // device skips the unused draw (Q24)
@@ -629,10 +699,12 @@ struct Tracer {
                 return att * color(Ray{rec.p, dir, r.time}, depth - 1, bounce + 1);
             }
             case RTW_MAT_DIELECTRIC: {
+                ev(EV_DIELECTRIC), ev(EV_SPECULAR_UPDATE);
                 V dir = dielectric_scatter(m, r, rec, bounce);
                 return mk(1.0, 1.0, 1.0) * color(Ray{rec.p, dir, r.time}, depth - 1, bounce + 1);
             }
             case RTW_MAT_ISOTROPIC: {  // material.h:257-262
+                ev(EV_ISOTROPIC), ev(EV_SPECULAR_UPDATE);
                 V dir = random_in_unit_sphere(rng, bounce);
                 V att = texture_value(fs, m.texture, rec.u, rec.v, rec.p);
                 return att * color(Ray{rec.p, dir, r.time}, depth - 1, bounce + 1);
@@ -653,6 +725,7 @@ struct Tracer {
             double r1, r2;
             if (rng.mode == MODE_MINSTD) r1 = rng.random_double(), r2 = rng.random_double();
             else r1 = pu[2], r2 = pu[3];
+            ev(EV_COSINE_GEN);
             dir = uvw.local(random_cosine_direction(r1, r2));  // pdf.h:26-29
         } else {
             int n = fs->n_lights;
@@ -671,6 +744,8 @@ struct Tracer {
             dir = light_random(l, rec.p, r1, r2);
         }
         Ray scattered{rec.p, dir, r.time};
+        ev(EV_COSINE_VALUE), ev(EV_SCATTERING_PDF), ev(EV_LAMBERT_UPDATE);
+        if (have_lights) ev(EV_MIXTURE);
         double cosine = dot(normalize(dir), uvw.w);  // cosine_pdf::value (pdf.h:20-24)
         double pdf_cos = (cosine <= 0) ? 0 : cosine / M_PI;
         double pdf_val = pdf_cos;
@@ -689,6 +764,8 @@ struct Tracer {
         V cu = mk(c.u[0], c.u[1], c.u[2]), cv = mk(c.v[0], c.v[1], c.v[2]);
         V rd;
         double time;
+        ev(EV_CAMERA);
+        if (c.lens_radius > 0) ev(EV_LENS);
         if (rng.mode == MODE_MINSTD) {
             V p;
             do {  // camera.h:61-69; the two constructor-argument draws happen right to left (y first)
@@ -717,7 +794,32 @@ struct Tracer {
 }  // namespace
 
 // ------------------------------------------------------------------------------------------------ C API (ctypes)
+namespace {
+bool g_events_on = false;
+uint64_t g_event_totals[EV_COUNT] = {0};
+// Appendix D cost table C_e (FMA = 2; add/mul/div/sqrt/transcendental = 1; compares, selects, integer = 0)
+const double kEventCost[EV_COUNT] = {
+    34, 25, 6, 12, 23, 4, 19, 12, 21, 3, 12, 3, 20, 21, 5, 36, 25, 15, 15, 3, 9, 43, 76, 60, 3, 12, 3, 48, 75, 21, 8, 7, 140,
+    7 * 6 + 1 + 5 /* noise_texture::value on top of its 7 perlin::noise calls */, 0};
+}  // namespace
+
 extern "C" {
+
+// Event accounting for the roofline: enable, render, then read counts and the flop total.
+void oracle_events_enable(int on) {
+    g_events_on = on != 0;
+    for (auto& t : g_event_totals) t = 0;
+}
+// out_counts[EV_COUNT] (may be null); returns sum_e N_e * C_e (algorithmic FP32 flops of the reference's math).
+double oracle_events_read(uint64_t* out_counts, int cap) {
+    double flops = 0;
+    for (int k = 0; k < EV_COUNT; k++) {
+        if (out_counts && k < cap) out_counts[k] = g_event_totals[k];
+        flops += (double)g_event_totals[k] * kEventCost[k];
+    }
+    return flops;
+}
+int oracle_event_count() { return EV_COUNT; }
 
 // world.hit() per ray, media skipped.  rays: n x 7 doubles (o, d, time).  out: n x 12 doubles
 // [hit, t, px, py, pz, nx, ny, nz, u, v, material, prim].
@@ -747,7 +849,9 @@ void oracle_render(const rtw_flat_scene* fs, int nx, int ny, int spp_begin, int 
     if (mode == MODE_MINSTD) threads = 1;
     if (threads < 1) threads = 1;
     std::vector<uint64_t> rays(threads, 0);
+    std::vector<std::vector<uint64_t>> evs(threads, std::vector<uint64_t>(EV_COUNT, 0));
     auto work = [&](int tid) {
+        g_ev = g_events_on ? evs[tid].data() : nullptr;
         Tracer tr{fs};
         tr.rng.mode = mode;
         tr.rng.seed_lo = (uint32_t)(seed & 0xffffffffu);
@@ -782,6 +886,7 @@ void oracle_render(const rtw_flat_scene* fs, int nx, int ny, int spp_begin, int 
                 }
             }
         rays[tid] = tr.rays;
+        g_ev = nullptr;
     };
     if (threads == 1) work(0);
     else {
@@ -792,6 +897,8 @@ void oracle_render(const rtw_flat_scene* fs, int nx, int ny, int spp_begin, int 
     uint64_t total = 0;
     for (uint64_t r : rays) total += r;
     if (out_rays) *out_rays = total;
+    for (auto& e : evs)
+        for (int k = 0; k < EV_COUNT; k++) g_event_totals[k] += e[k];
 }
 
 int oracle_hardware_threads() { return (int)std::thread::hardware_concurrency(); }
@@ -946,4 +1053,24 @@ extern "C" int oracle_funcs(const double* tables, double* out, int cap) {
     int n = (int)std::min<size_t>(o.size(), (size_t)cap);
     memcpy(out, o.data(), n * sizeof(double));
     return (int)o.size();
+}
+
+// CppTest/unittest1.cpp:20-40, 72-109 restated on this file's vec3/ray/aabb forms.  out[22]:
+// dot, cross(3), point_at_parameter(3), aabb hits(5), surrounding min(3), max(3), sizeof(vec3), reserved(3)
+extern "C" void oracle_kat(double* out) {
+    int k = 0;
+    out[k++] = dot(mk(1, 1, 0), mk(1, 1, 0));
+    V c = cross(mk(1, 0, 0), mk(0, 1, 0));
+    out[k++] = c.x, out[k++] = c.y, out[k++] = c.z;
+    Ray r{mk(1, 1, 1), mk(2, 2, 2), 0.0};
+    V p = r.at(3);
+    out[k++] = p.x, out[k++] = p.y, out[k++] = p.z;
+    double mn[3] = {2, 2, 2}, mx[3] = {4, 4, 4};
+    Ray cases[5] = {{mk(0, 0, 0), mk(1, 1, 1), 0}, {mk(0, 0, 0), -mk(1, 1, 1), 0}, {mk(3, 3, 3), mk(0, 1, 0), 0},
+                    {mk(0, 3, 0), mk(1, 0, 1), 0}, {mk(0, 5, 0), mk(1, 0, 1), 0}};
+    for (auto& q : cases) out[k++] = aabb_hit(mn, mx, q, 0, FLT_MAX) ? 1 : 0;
+    double a0[3] = {0, 0, 0}, a1[3] = {1, 1, 1}, b0[3] = {3, 3, 3}, b1[3] = {4, 4, 4};
+    for (int i = 0; i < 3; i++) out[k++] = fmin(a0[i], b0[i]);  // aabb.h:49-62
+    for (int i = 0; i < 3; i++) out[k++] = fmax(a1[i], b1[i]);
+    out[k++] = (double)sizeof(V);
 }

@@ -134,6 +134,7 @@ SIGNATURES = {
     "rtw_tonemap": (C.c_int, [_P, C.c_int, C.c_int, _P]),
     "rtw_write_ppm": (C.c_int, [C.c_char_p, _P, C.c_int, C.c_int]),
     "rtw_device_count": (C.c_int, []),
+    "rtw_measure_fp32_peak": (C.c_int, [C.c_int, C.POINTER(C.c_double)]),
 }
 
 _lib = None

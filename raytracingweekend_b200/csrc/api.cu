@@ -427,3 +427,14 @@ extern "C" int rtw_intersect_batch(rtw_scene* s, const rtw_ray* rays, rtw_hit* h
     if (d_hits) cudaFree(d_hits);
     return rc;
 }
+
+extern "C" int rtw_measure_fp32_peak(int device, double* tflops) {
+    if (!tflops) {
+        set_error("measure_fp32_peak: null");
+        return RTW_ERR_INVALID;
+    }
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
+    if ((e = measure_fp32_peak(tflops)) != cudaSuccess) return cuda_fail(e, "fp32 peak probe");
+    return RTW_OK;
+}

@@ -91,7 +91,7 @@ __global__ void __launch_bounds__(kBlock) intersect_kernel(const __grid_constant
     if (idx >= n) return;
     rtw_ray r = rays[idx];
     V3 o = mk(r.ox, r.oy, r.oz), d = mk(r.dx, r.dy, r.dz);
-    HitId h = closest_hit<F>(sc, o, d, r.time, tmin, tmax, nullptr, 0, stack, kBlock);
+    HitId h = closest_hit<F, true>(sc, o, d, r.time, tmin, tmax, nullptr, 0, stack, kBlock);
     rtw_hit out;
     if (h.prim < 0) {
         out.prim = -1, out.material = -1;
@@ -155,4 +155,53 @@ cudaError_t launch_intersect(const DevScene& sc, const rtw_ray* rays, rtw_hit* h
     }
 }
 
+}  // namespace rtw
+
+// ------------------------------------------------------------------------------------------------ FP32 peak probe
+// Roofline denominator: dependent-chain-free FFMA throughput measured in the same session.
+namespace rtw {
+__global__ void __launch_bounds__(256) fma_peak_kernel(float* out, int iters) {
+    float a[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) a[k] = 1.0f + 1e-3f * (float)(threadIdx.x + k);
+    const float m = 0.9999f, c = 1e-4f;
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int k = 0; k < 16; k++) a[k] = fmaf(a[k], m, c);
+    }
+    float s = 0.0f;
+#pragma unroll
+    for (int k = 0; k < 16; k++) s += a[k];
+    if (s == 123.456f) out[0] = s;  // keep the chains alive
+}
+
+cudaError_t measure_fp32_peak(double* tflops) {
+    float* d = nullptr;
+    cudaError_t e = cudaMalloc(&d, sizeof(float));
+    if (e != cudaSuccess) return e;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    int sms = 0;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int iters = 1 << 14, blocks = sms * 8, threads = 256;
+    double best = 0.0;
+    for (int rep = 0; rep < 4; rep++) {
+        cudaEventRecord(e0);
+        fma_peak_kernel<<<blocks, threads>>>(d, iters);
+        cudaEventRecord(e1);
+        if ((e = cudaEventSynchronize(e1)) != cudaSuccess) break;
+        float ms = 0;
+        cudaEventElapsedTime(&ms, e0, e1);
+        double fl = 2.0 * 16.0 * iters * (double)blocks * threads;
+        if (rep > 0 && ms > 0) best = fmax(best, fl / (ms * 1e-3) / 1e12);
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(d);
+    *tflops = best;
+    return e;
+}
 }  // namespace rtw

@@ -16,4 +16,7 @@ cudaError_t launch_render(const DevScene& sc, const DevRenderParams& rp, float4*
 cudaError_t launch_intersect(const DevScene& sc, const rtw_ray* rays, rtw_hit* hits, long long n, float tmin, float tmax,
                              cudaStream_t st);
 
+// FFMA throughput of the current device in TFLOP/s (roofline denominator, measured not assumed).
+cudaError_t measure_fp32_peak(double* tflops);
+
 }  // namespace rtw

@@ -14,7 +14,7 @@ template <uint32_t F>
 RTW_DEV bool path_step(const DevScene& sc, const Rng& rng, uint32_t bounce, Ray& ray, V3& beta, V3& L, int* stack,
                        int stride) {
     // :52 world.hit(r, 0.001f, DBL_MAX, rec)
-    HitId h = closest_hit<F>(sc, ray.o, ray.d, ray.time, 0.001f, FLT_MAX, &rng, bounce, stack, stride);
+    HitId h = closest_hit<F, false>(sc, ray.o, ray.d, ray.time, 0.001f, FLT_MAX, &rng, bounce, stack, stride);
     if (h.prim == -1) {  // :141-159
         L = L + beta * background(sc, ray.d);
         return false;

