@@ -196,8 +196,13 @@ def test_render_type_normal(scenes):
     sc = rtw.Scene(b)
     acc, st = sc.render(32, 32, 4, seed=1)
     assert st["rays"] == st["paths"]
-    centre = acc[16, 16, :3] / 4  # back wall, flipped xy_rect: normal (0,0,-1) -> 0.5*(n+1) = (0.5, 0.5, 0)
-    assert np.allclose(centre, (0.5, 0.5, 0.0), atol=1e-6)
+    # pixel (i=16, j=22) is on the back wall above the tall box (the centre pixel straddles the box edge):
+    # flipped xy_rect, normal (0,0,-1) -> 0.5*(n+1) = (0.5, 0.5, 0)
+    wall = acc[22, 16, :3] / 4
+    assert np.allclose(wall, (0.5, 0.5, 0.0), atol=1e-6)
+    # floor pixel: xz_rect y=0, normal (0,1,0) -> (0.5, 1, 0.5)
+    floor = acc[2, 16, :3] / 4
+    assert np.allclose(floor, (0.5, 1.0, 0.5), atol=1e-6)
 
 
 def test_device_pointer_api_with_torch(scenes):
