@@ -6,7 +6,8 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "lib", "librtw_b200.so")
+# RTW_B200_LIB: alternative build of the same library (kernel tuning experiments); never a CPU fallback
+LIB_PATH = os.environ.get("RTW_B200_LIB") or os.path.join(HERE, "lib", "librtw_b200.so")
 
 RTW_OK = 0
 RTW_FLAG_WAVEFRONT = 1

@@ -21,6 +21,8 @@ HOST_SRCS = ["builder.cpp", "scenes.cpp", "hostio.cpp"]
 CUDA_SRCS = ["kernels.cu", "api.cu"]
 NVCC_ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 CXXFLAGS = ["-std=c++17", "-O2", "-fPIC", "-Wall"]
+# FP32 division / sqrt as reciprocal-multiply and MUFU forms (2 ulp), denormals flushed; sin/cos/log/exp stay accurate
+NVCC_MATH = ["-prec-div=false", "-prec-sqrt=false", "-ftz=true"]
 
 
 def _nvcc() -> str:
@@ -50,7 +52,7 @@ def _headers() -> list[str]:
     return hs
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
+def build(force: bool = False, verbose: bool = False, extra: list[str] | None = None, tag: str = "") -> str:
     """Compile everything that is out of date; returns the path of librtw_b200.so."""
     os.makedirs(LIB, exist_ok=True)
     os.makedirs(OBJ, exist_ok=True)
@@ -67,14 +69,14 @@ def build(force: bool = False, verbose: bool = False) -> str:
     nvcc = _nvcc()
     cuda_objs = []
     for s in CUDA_SRCS:
-        src, obj = os.path.join(CSRC, s), os.path.join(OBJ, s + ".o")
+        src, obj = os.path.join(CSRC, s), os.path.join(OBJ, s + tag + ".o")
         if force or _stale(obj, [src] + hdrs):
-            cmd = [nvcc, *NVCC_ARCH, "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC", "-c", src, "-o", obj]
+            cmd = [nvcc, *NVCC_ARCH, "-O3", "-lineinfo", "-std=c++17", *NVCC_MATH, *(extra or []), "-Xcompiler", "-fPIC", "-c", src, "-o", obj]
             if verbose:
                 cmd.insert(1, "-Xptxas=-v")
             _run(cmd)
         cuda_objs.append(obj)
-    full_so = os.path.join(LIB, "librtw_b200.so")
+    full_so = os.path.join(LIB, f"librtw_b200{tag}.so")
     if force or _stale(full_so, host_objs + cuda_objs):
         _run([nvcc, *NVCC_ARCH, "-shared", "-o", full_so, *host_objs, *cuda_objs, "-cudart", "static"])
     return full_so

@@ -70,7 +70,7 @@ int bvh_depth(const rtw_flat_scene* fs, int ref, int depth) {
 struct rtw_scene {
     int device = 0;
     DevScene dev{};
-    DevBuf items, pa, pb, pm, pd, xfs, node_lo, node_hi, leaves, mats, texs, texels, ranvec, perm, lights;
+    DevBuf blob, texels;
     unsigned long long* d_counter = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     // pending asynchronous render
@@ -80,8 +80,8 @@ struct rtw_scene {
     float* scratch_accum = nullptr;  // device buffer behind rtw_render (host API)
     size_t scratch_pixels = 0;
     void release() {
-        DevBuf* all[] = {&items, &pa, &pb, &pm, &pd, &xfs, &node_lo, &node_hi, &leaves, &mats, &texs, &texels, &ranvec, &perm, &lights};
-        for (DevBuf* b : all) b->release();
+        blob.release();
+        texels.release();
         if (d_counter) cudaFree(d_counter);
         if (scratch_accum) cudaFree(scratch_accum);
         if (ev0) cudaEventDestroy(ev0);
@@ -170,6 +170,48 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
         pm[i] = m;
     }
 
+    // primitive-test groups and records (device_scene.hpp): split a run of primitives into maximal runs that
+    // share a transform chain, and order each run's records spheres, moving spheres, xy, xz, yz rects.
+    std::vector<DevGroup> groups;
+    std::vector<DevRec> recs;
+    auto add_groups = [&](int first, int count, int& first_group, int& n_groups) {
+        first_group = (int)groups.size();
+        int i = first;
+        while (i < first + count) {
+            int j = i;
+            while (j < first + count && fs->prims[j].xf == fs->prims[i].xf) j++;
+            DevGroup g{};
+            g.xf = fs->prims[i].xf;
+            g.sph0 = (int)recs.size();
+            const int kinds[5] = {RTW_PRIM_SPHERE, RTW_PRIM_MOVING_SPHERE, RTW_PRIM_XY_RECT, RTW_PRIM_XZ_RECT, RTW_PRIM_YZ_RECT};
+            int32_t* ends[5] = {&g.sph1, &g.msph1, &g.xy1, &g.xz1, &g.yz1};
+            for (int k = 0; k < 5; k++) {
+                for (int p = i; p < j; p++) {
+                    if (fs->prims[p].type != kinds[k]) continue;
+                    DevRec r{};
+                    r.a = pa[p];
+                    if (k == 0) {
+                        int id = p;
+                        if (pm[p] & PM_PRECISE) {
+                            id |= REC_PRECISE;
+                            r.b.x = pb[p].w;  // pd index bits
+                        }
+                        r.b.w = __int_as_float_host(id);
+                    } else if (k == 1) {
+                        r.b = make_float4(pb[p].x, pb[p].y, pb[p].z, __int_as_float_host(p));
+                    } else {
+                        r.b = make_float4(pb[p].x, 0.0f, 0.0f, __int_as_float_host(p));
+                    }
+                    recs.push_back(r);
+                }
+                *ends[k] = (int)recs.size();
+            }
+            groups.push_back(g);
+            i = j;
+        }
+        n_groups = (int)groups.size() - first_group;
+    };
+
     std::vector<DevItem> items(fs->n_items);
     int max_depth = 0;
     for (int i = 0; i < fs->n_items; i++) {
@@ -182,6 +224,8 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
             feat |= F_BVH;
             int dep = bvh_depth(fs, it.first, 0);
             if (dep > max_depth) max_depth = dep;
+        } else {
+            add_groups(it.first, it.count, d.first, d.count);
         }
         if (it.type == RTW_ITEM_MEDIUM) feat |= F_MEDIA;
         items[i] = d;
@@ -198,7 +242,7 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
         node_hi[i] = make_float4((float)n.bmax[0], (float)n.bmax[1], (float)n.bmax[2], __int_as_float_host(n.right));
     }
     std::vector<int2> leaves(fs->n_leaves);
-    for (int i = 0; i < fs->n_leaves; i++) leaves[i] = make_int2(fs->leaves[i].first_prim, fs->leaves[i].prim_count);
+    for (int i = 0; i < fs->n_leaves; i++) add_groups(fs->leaves[i].first_prim, fs->leaves[i].prim_count, leaves[i].x, leaves[i].y);
 
     std::vector<DevTex> texs(fs->n_textures);
     for (int i = 0; i < fs->n_textures; i++) {
@@ -251,13 +295,38 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
     std::vector<uint8_t> texels;
     if (fs->n_texel_bytes) texels.assign(fs->texels, fs->texels + fs->n_texel_bytes);
 
+    // pack the blob: 16-byte aligned sections, hot first
+    std::vector<uint8_t> blob;
+    uint32_t off[SEC_COUNT] = {};
+    auto put = [&](int sec, const void* data, size_t bytes) {
+        off[sec] = (uint32_t)blob.size();
+        const uint8_t* p = (const uint8_t*)data;
+        if (bytes) blob.insert(blob.end(), p, p + bytes);
+        blob.resize((blob.size() + 15) & ~(size_t)15, 0);
+    };
+    put(SEC_ITEMS, items.data(), items.size() * sizeof(DevItem));
+    put(SEC_GROUPS, groups.data(), groups.size() * sizeof(DevGroup));
+    put(SEC_RECS, recs.data(), recs.size() * sizeof(DevRec));
+    put(SEC_XFS, xfs.data(), xfs.size() * sizeof(DevXf));
+    put(SEC_LIGHTS, lights.data(), lights.size() * sizeof(DevLight));
+    put(SEC_NODE_LO, node_lo.data(), node_lo.size() * sizeof(float4));
+    put(SEC_NODE_HI, node_hi.data(), node_hi.size() * sizeof(float4));
+    put(SEC_LEAVES, leaves.data(), leaves.size() * sizeof(int2));
+    uint32_t hot_bytes = (uint32_t)blob.size();
+    put(SEC_PM, pm.data(), pm.size() * sizeof(uint32_t));
+    put(SEC_PA, pa.data(), pa.size() * sizeof(float4));
+    put(SEC_PB, pb.data(), pb.size() * sizeof(float4));
+    put(SEC_PD, pd.data(), pd.size() * sizeof(double));
+    put(SEC_MATS, mats.data(), mats.size() * sizeof(DevMat));
+    put(SEC_TEXS, texs.data(), texs.size() * sizeof(DevTex));
+    put(SEC_RANVEC, ranvec.data(), ranvec.size() * sizeof(float4));
+    put(SEC_PERM, perm.data(), perm.size());
+    if (blob.empty()) blob.resize(16, 0);
+
     rtw_scene* s = new (std::nothrow) rtw_scene();
     if (!s) return nullptr;
     s->device = device;
-    cudaError_t err[] = {s->items.upload(items), s->pa.upload(pa), s->pb.upload(pb), s->pm.upload(pm), s->pd.upload(pd),
-                         s->xfs.upload(xfs), s->node_lo.upload(node_lo), s->node_hi.upload(node_hi), s->leaves.upload(leaves),
-                         s->mats.upload(mats), s->texs.upload(texs), s->texels.upload(texels), s->ranvec.upload(ranvec),
-                         s->perm.upload(perm), s->lights.upload(lights), cudaMalloc(&s->d_counter, sizeof(unsigned long long)),
+    cudaError_t err[] = {s->blob.upload(blob), s->texels.upload(texels), cudaMalloc(&s->d_counter, sizeof(unsigned long long)),
                          cudaEventCreate(&s->ev0), cudaEventCreate(&s->ev1)};
     for (cudaError_t x : err)
         if (x != cudaSuccess) {
@@ -267,12 +336,9 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
             return nullptr;
         }
     DevScene& d = s->dev;
-    d.items = (const DevItem*)s->items.p, d.pa = (const float4*)s->pa.p, d.pb = (const float4*)s->pb.p;
-    d.pm = (const uint32_t*)s->pm.p, d.pd = (const double*)s->pd.p, d.xfs = (const DevXf*)s->xfs.p;
-    d.node_lo = (const float4*)s->node_lo.p, d.node_hi = (const float4*)s->node_hi.p, d.leaves = (const int2*)s->leaves.p;
-    d.mats = (const DevMat*)s->mats.p, d.texs = (const DevTex*)s->texs.p, d.texels = (const uint8_t*)s->texels.p;
-    d.perlin_ranvec = (const float4*)s->ranvec.p, d.perlin_perm = (const uint8_t*)s->perm.p;
-    d.lights = (const DevLight*)s->lights.p;
+    d.blob = (const uint8_t*)s->blob.p, d.texels = (const uint8_t*)s->texels.p;
+    for (int k = 0; k < SEC_COUNT; k++) d.off[k] = off[k];
+    d.hot_bytes = hot_bytes, d.all_bytes = (uint32_t)blob.size();
     d.n_world_items = fs->n_world_items, d.n_items = fs->n_items, d.n_prims = fs->n_prims, d.n_lights = fs->n_lights;
     d.render_type = fs->render_type, d.background_type = fs->background_type;
     d.features = feat, d.max_bvh_depth = max_depth;

@@ -1,8 +1,19 @@
 // device_scene.hpp — FP32 device-resident form of `rtw_flat_scene` (HBM layout).
 //
-// All arrays live in global memory and are read through the read-only path (ld.global.nc, 16-byte
-// vectors).  In the linear-list loops every lane of a warp reads the SAME element, so each load is one
-// broadcast transaction served by L1; BVH nodes are the only divergent reads.
+// The whole scene except image texels is ONE packed blob of 16-byte aligned sections, ordered hot-first:
+//
+//   [ items | groups | recs | xfs | lights | node_lo | node_hi | leaves ]   <- "hot": touched per primitive test
+//   [ pm | pa | pb | pd | mats | texs | perlin_ranvec | perlin_perm ]       <- "cold": touched once per ray
+//
+// A render block stages a prefix of the blob into shared memory (everything, the hot part, or nothing,
+// depending on its size) and walks it with warp-uniform indices, so every primitive-test load is a shared
+// memory broadcast; larger scenes read the same sections from global memory through L1 (ld.global.nc).
+//
+// Primitive tests are driven by `DevGroup`s: a group is a run of primitives of one item that share a
+// transform chain, re-ordered by kind (spheres, moving spheres, xy/xz/yz rects) so the inner loops are
+// branch-free per kind.  The reference's list-order tie rules survive the re-ordering because they
+// can be stated order-independently: among equal t a rect beats a sphere, the later rect beats the earlier
+// rect, the earlier sphere beats the later sphere — and spheres-then-rects in index order evaluates exactly that.
 #pragma once
 #include <cstdint>
 #include <cuda_runtime.h>
@@ -25,11 +36,27 @@ struct DevXf {
 };
 
 struct DevItem {
-    int32_t type, xf, first, count;  // xf: index into xfs or -1
+    int32_t type, xf, first, count;  // xf: index into xfs or -1; PRIMS/MEDIUM: first/count are GROUPS; BVH: first = root node
     int32_t material, flip;
     float density_eff;  // density * multiplicity
     float pad;
 };
+
+// Run of primitive-test records sharing one transform chain (xf = index into xfs, or -1).
+// recs[sph0, sph1) spheres; [sph1, msph1) moving spheres; [msph1, xy1) xy_rects; [xy1, xz1) xz_rects; [xz1, yz1) yz_rects.
+struct DevGroup {
+    int32_t xf, sph0, sph1, msph1;
+    int32_t xy1, xz1, yz1, pad;
+};
+
+// One primitive-test record (32 bytes = two 16-byte loads).
+//   sphere:        a = (cx, cy, cz, radius)        b = (pd index bits, -, -, prim id | REC_PRECISE)
+//   moving sphere: a = (c'x, c'y, c'z, radius)     b = (dx, dy, dz, prim id)     centre(time) = c' + time*d
+//   rect:          a = (a0, a1, b0, b1)            b = (k, -, -, prim id)
+struct DevRec {
+    float4 a, b;
+};
+constexpr int32_t REC_PRECISE = 1 << 30;
 
 struct DevMat {
     float r, g, b, param;  // metal: albedo + fuzz; dielectric: param = ref_idx; textured: resolved constant colour
@@ -63,22 +90,17 @@ enum : uint32_t {  // feature mask -> kernel specialisation
     F_ALL = 0x3Fu
 };
 
+enum {  // blob sections, in blob order
+    SEC_ITEMS = 0, SEC_GROUPS, SEC_RECS, SEC_XFS, SEC_LIGHTS, SEC_NODE_LO, SEC_NODE_HI, SEC_LEAVES,  // hot
+    SEC_PM, SEC_PA, SEC_PB, SEC_PD, SEC_MATS, SEC_TEXS, SEC_RANVEC, SEC_PERM,                       // cold
+    SEC_COUNT
+};
+
 struct DevScene {
-    const DevItem* items;
-    const float4* pa;
-    const float4* pb;
-    const uint32_t* pm;
-    const double* pd;  // 4 doubles per precise sphere (cx cy cz r); index in pb.w bits
-    const DevXf* xfs;
-    const float4* node_lo;  // bmin.xyz, left (int bits)
-    const float4* node_hi;  // bmax.xyz, right (int bits)
-    const int2* leaves;
-    const DevMat* mats;
-    const DevTex* texs;
-    const uint8_t* texels;
-    const float4* perlin_ranvec;
-    const uint8_t* perlin_perm;  // 3*256
-    const DevLight* lights;
+    const uint8_t* blob;   // global memory, 16-byte aligned
+    const uint8_t* texels;  // RGB8 image texels (global only)
+    uint32_t off[SEC_COUNT];  // byte offset of each section inside the blob
+    uint32_t hot_bytes, all_bytes;  // blob prefix sizes (multiples of 16)
     int32_t n_world_items, n_items, n_prims, n_lights;
     int32_t render_type, background_type;
     uint32_t features;
@@ -90,6 +112,27 @@ struct DevRenderParams {
     int32_t nx, ny, spp_begin, spp_count, max_depth;
     uint32_t flags;
     uint32_t seed_lo, seed_hi;
+};
+
+// Typed view of the blob: pointers into shared memory for the staged prefix, into global memory otherwise.
+struct SceneView {
+    const DevItem* items;
+    const DevGroup* groups;
+    const DevRec* recs;
+    const DevXf* xfs;
+    const DevLight* lights;
+    const float4* node_lo;  // bmin.xyz, left (int bits)
+    const float4* node_hi;  // bmax.xyz, right (int bits)
+    const int2* leaves;     // (first group, group count)
+    const uint32_t* pm;
+    const float4* pa;
+    const float4* pb;
+    const double* pd;  // 4 doubles per precise sphere (cx cy cz r)
+    const DevMat* mats;
+    const DevTex* texs;
+    const float4* perlin_ranvec;
+    const uint8_t* perlin_perm;  // 3*256
+    const uint8_t* texels;
 };
 
 }  // namespace rtw

@@ -11,16 +11,60 @@
 namespace rtw {
 
 constexpr int kBlock = 128;   // 4 warps
+#ifndef RTW_MIN_BLOCKS
+#define RTW_MIN_BLOCKS 6  // resident blocks per SM the register allocator must allow (tuned from ncu)
+#endif
 constexpr int kTileW = 16;    // block tile: 16 x 8 pixels, warp tile 8 x 4
 constexpr int kTileH = 8;
 
-template <uint32_t F>
-__global__ void __launch_bounds__(kBlock) render_megakernel(const __grid_constant__ DevScene sc,
+// Stage the first `bytes` of the scene blob into shared memory (16-byte vectors, whole block) and build the typed view.
+template <int SM>
+RTW_DEV SceneView stage_scene(const DevScene& sc, uint4* smem) {
+    const uint32_t staged = SM == 2 ? sc.all_bytes : (SM == 1 ? sc.hot_bytes : 0u);
+    if (SM > 0) {
+        const uint4* src = reinterpret_cast<const uint4*>(sc.blob);
+        for (uint32_t i = threadIdx.x; i < staged / 16; i += blockDim.x) smem[i] = __ldg(src + i);
+        __syncthreads();
+    }
+    const uint8_t* sm = reinterpret_cast<const uint8_t*>(smem);
+    const uint8_t* gm = sc.blob;
+    SceneView v;
+#define RTW_SEC(field, type, sec, hot) \
+    v.field = reinterpret_cast<const type*>(((SM == 2) || (SM == 1 && hot)) ? sm + sc.off[sec] : gm + sc.off[sec]);
+    RTW_SEC(items, DevItem, SEC_ITEMS, true)
+    RTW_SEC(groups, DevGroup, SEC_GROUPS, true)
+    RTW_SEC(recs, DevRec, SEC_RECS, true)
+    RTW_SEC(xfs, DevXf, SEC_XFS, true)
+    RTW_SEC(lights, DevLight, SEC_LIGHTS, true)
+    RTW_SEC(node_lo, float4, SEC_NODE_LO, true)
+    RTW_SEC(node_hi, float4, SEC_NODE_HI, true)
+    RTW_SEC(leaves, int2, SEC_LEAVES, true)
+    RTW_SEC(pm, uint32_t, SEC_PM, false)
+    RTW_SEC(pa, float4, SEC_PA, false)
+    RTW_SEC(pb, float4, SEC_PB, false)
+    RTW_SEC(pd, double, SEC_PD, false)
+    RTW_SEC(mats, DevMat, SEC_MATS, false)
+    RTW_SEC(texs, DevTex, SEC_TEXS, false)
+    RTW_SEC(perlin_ranvec, float4, SEC_RANVEC, false)
+    RTW_SEC(perlin_perm, uint8_t, SEC_PERM, false)
+#undef RTW_SEC
+    v.texels = sc.texels;
+    return v;
+}
+// dynamic shared memory: [staged blob prefix][BVH traversal stacks]
+RTW_DEV int* stack_base(const DevScene& sc, int sm_level, uint4* smem) {
+    uint32_t staged = sm_level == 2 ? sc.all_bytes : (sm_level == 1 ? sc.hot_bytes : 0u);
+    return reinterpret_cast<int*>(reinterpret_cast<uint8_t*>(smem) + staged);
+}
+
+template <uint32_t F, int SM>
+__global__ void __launch_bounds__(kBlock, RTW_MIN_BLOCKS) render_megakernel(const __grid_constant__ DevScene sc,
                                                            const __grid_constant__ DevRenderParams rp,
                                                            float4* __restrict__ accum,
                                                            unsigned long long* __restrict__ ray_counter) {
-    __shared__ int s_stack[(F & F_BVH) ? kStackDepth * kBlock : 1];
-    int* stack = s_stack + threadIdx.x;
+    extern __shared__ uint4 smem[];
+    const SceneView sv = stage_scene<SM>(sc, smem);
+    int* stack = stack_base(sc, SM, smem) + threadIdx.x;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int tiles_x = (rp.nx + kTileW - 1) / kTileW;
@@ -63,7 +107,7 @@ __global__ void __launch_bounds__(kBlock) render_megakernel(const __grid_constan
             }
             bounce++;
             rays++;
-            alive = path_step<F>(sc, rng, bounce, ray, beta, L, stack, kBlock);
+            alive = path_step<F, SM>(sc, sv, rng, bounce, ray, beta, L, stack, kBlock);
             if (alive && (int)bounce >= rp.max_depth) alive = false;  // :47-48: the next color() returns 0
             if (!alive) sum = sum + L;                                // :235-239
         }
@@ -81,23 +125,24 @@ __global__ void __launch_bounds__(kBlock) render_megakernel(const __grid_constan
 }
 
 // world.hit() on a fixed ray batch (parity tiers 1-2): one thread per ray, media skipped.
-template <uint32_t F>
+template <uint32_t F, int SM>
 __global__ void __launch_bounds__(kBlock) intersect_kernel(const __grid_constant__ DevScene sc,
                                                           const rtw_ray* __restrict__ rays, rtw_hit* __restrict__ hits,
                                                           long long n, float tmin, float tmax) {
-    __shared__ int s_stack[(F & F_BVH) ? kStackDepth * kBlock : 1];
-    int* stack = s_stack + threadIdx.x;
+    extern __shared__ uint4 smem[];
+    const SceneView sv = stage_scene<SM>(sc, smem);
+    int* stack = stack_base(sc, SM, smem) + threadIdx.x;
     long long idx = (long long)blockIdx.x * kBlock + threadIdx.x;
     if (idx >= n) return;
     rtw_ray r = rays[idx];
     V3 o = mk(r.ox, r.oy, r.oz), d = mk(r.dx, r.dy, r.dz);
-    HitId h = closest_hit<F, true>(sc, o, d, r.time, tmin, tmax, nullptr, 0, stack, kBlock);
+    HitId h = closest_hit<F, SM, true>(sc, sv, o, d, r.time, tmin, tmax, nullptr, 0, stack, kBlock);
     rtw_hit out;
     if (h.prim < 0) {
         out.prim = -1, out.material = -1;
         out.t = out.u = out.v = out.nx = out.ny = out.nz = 0.0f;
     } else {
-        HitRec rec = complete_hit<F>(sc, h, o, d, r.time, true);
+        HitRec rec = complete_hit<F, SM>(sv, h, o, d, r.time, true);
         out.prim = h.prim, out.material = rec.mat;
         out.t = h.t, out.u = rec.u, out.v = rec.v;
         out.nx = rec.n.x, out.ny = rec.n.y, out.nz = rec.n.z;
@@ -107,21 +152,9 @@ __global__ void __launch_bounds__(kBlock) intersect_kernel(const __grid_constant
 
 // ------------------------------------------------------------------------------------------------ launchers
 // Kernel specialisations: the smallest feature superset is chosen per scene (registers and code size shrink
-// a lot when BVH / media / textures are compiled out, e.g. for the Cornell box).
-template <uint32_t F>
-static cudaError_t launch_render_t(const DevScene& sc, const DevRenderParams& rp, float4* accum,
-                                   unsigned long long* counter, cudaStream_t st) {
-    int tiles_x = (rp.nx + kTileW - 1) / kTileW, tiles_y = (rp.ny + kTileH - 1) / kTileH;
-    render_megakernel<F><<<tiles_x * tiles_y, kBlock, 0, st>>>(sc, rp, accum, counter);
-    return cudaGetLastError();
-}
-template <uint32_t F>
-static cudaError_t launch_intersect_t(const DevScene& sc, const rtw_ray* rays, rtw_hit* hits, long long n, float tmin,
-                                      float tmax, cudaStream_t st) {
-    long long blocks = (n + kBlock - 1) / kBlock;
-    intersect_kernel<F><<<(unsigned)blocks, kBlock, 0, st>>>(sc, rays, hits, n, tmin, tmax);
-    return cudaGetLastError();
-}
+// a lot when BVH / media / textures are compiled out, e.g. for the Cornell box), and the staging level from the
+// blob size: everything in shared memory (<= kStageMax), the hot sections only, or nothing.
+constexpr uint32_t kStageMax = 24 * 1024;  // per block; keeps >= 8 blocks of 128 threads resident per SM
 
 constexpr uint32_t kVariants[] = {
     F_XF,                                       // Cornell box, dielectric_scene
@@ -134,25 +167,79 @@ uint32_t pick_variant(uint32_t features) {
         if ((features & ~v) == 0) return v;
     return F_ALL;
 }
+int pick_stage(const DevScene& sc) {
+    if (sc.all_bytes <= kStageMax) return 2;
+    if (sc.hot_bytes <= kStageMax) return 1;
+    return 0;
+}
+
+namespace {
+struct Launch {
+    uint32_t variant;
+    int stage;
+    size_t smem;
+};
+Launch plan(const DevScene& sc) {
+    Launch l;
+    l.stage = pick_stage(sc);
+    l.variant = pick_variant(sc.features);
+    // instantiated combinations: every variant at stage 2; {moving, all} at stage 1; {all} at stage 0
+    if (l.stage == 1 && l.variant != kVariants[1]) l.variant = F_ALL;
+    if (l.stage == 0) l.variant = F_ALL;
+    size_t staged = l.stage == 2 ? sc.all_bytes : (l.stage == 1 ? sc.hot_bytes : 0);
+    size_t stack = (l.variant & F_BVH) ? (size_t)kStackDepth * kBlock * sizeof(int) : 0;
+    l.smem = staged + stack;
+    return l;
+}
+
+template <uint32_t F, int SM>
+cudaError_t launch_render_t(const DevScene& sc, const DevRenderParams& rp, float4* accum, unsigned long long* counter,
+                            size_t smem, cudaStream_t st) {
+    int tiles_x = (rp.nx + kTileW - 1) / kTileW, tiles_y = (rp.ny + kTileH - 1) / kTileH;
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(render_megakernel<F, SM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+    }
+    render_megakernel<F, SM><<<tiles_x * tiles_y, kBlock, smem, st>>>(sc, rp, accum, counter);
+    return cudaGetLastError();
+}
+template <uint32_t F, int SM>
+cudaError_t launch_intersect_t(const DevScene& sc, const rtw_ray* rays, rtw_hit* hits, long long n, float tmin, float tmax,
+                               size_t smem, cudaStream_t st) {
+    long long blocks = (n + kBlock - 1) / kBlock;
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(intersect_kernel<F, SM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+    }
+    intersect_kernel<F, SM><<<(unsigned)blocks, kBlock, smem, st>>>(sc, rays, hits, n, tmin, tmax);
+    return cudaGetLastError();
+}
+}  // namespace
+
+#define RTW_DISPATCH(FN, ...)                                                                      \
+    do {                                                                                           \
+        Launch l = plan(sc);                                                                       \
+        if (l.stage == 2) {                                                                        \
+            if (l.variant == kVariants[0]) return FN<kVariants[0], 2>(__VA_ARGS__, l.smem, st);    \
+            if (l.variant == kVariants[1]) return FN<kVariants[1], 2>(__VA_ARGS__, l.smem, st);    \
+            if (l.variant == kVariants[2]) return FN<kVariants[2], 2>(__VA_ARGS__, l.smem, st);    \
+            return FN<F_ALL, 2>(__VA_ARGS__, l.smem, st);                                          \
+        }                                                                                          \
+        if (l.stage == 1) {                                                                        \
+            if (l.variant == kVariants[1]) return FN<kVariants[1], 1>(__VA_ARGS__, l.smem, st);    \
+            return FN<F_ALL, 1>(__VA_ARGS__, l.smem, st);                                          \
+        }                                                                                          \
+        return FN<F_ALL, 0>(__VA_ARGS__, l.smem, st);                                              \
+    } while (0)
 
 cudaError_t launch_render(const DevScene& sc, const DevRenderParams& rp, float4* accum, unsigned long long* counter,
                           cudaStream_t st) {
-    switch (pick_variant(sc.features)) {
-        case kVariants[0]: return launch_render_t<kVariants[0]>(sc, rp, accum, counter, st);
-        case kVariants[1]: return launch_render_t<kVariants[1]>(sc, rp, accum, counter, st);
-        case kVariants[2]: return launch_render_t<kVariants[2]>(sc, rp, accum, counter, st);
-        default: return launch_render_t<F_ALL>(sc, rp, accum, counter, st);
-    }
+    RTW_DISPATCH(launch_render_t, sc, rp, accum, counter);
 }
 
 cudaError_t launch_intersect(const DevScene& sc, const rtw_ray* rays, rtw_hit* hits, long long n, float tmin, float tmax,
                              cudaStream_t st) {
-    switch (pick_variant(sc.features)) {
-        case kVariants[0]: return launch_intersect_t<kVariants[0]>(sc, rays, hits, n, tmin, tmax, st);
-        case kVariants[1]: return launch_intersect_t<kVariants[1]>(sc, rays, hits, n, tmin, tmax, st);
-        case kVariants[2]: return launch_intersect_t<kVariants[2]>(sc, rays, hits, n, tmin, tmax, st);
-        default: return launch_intersect_t<F_ALL>(sc, rays, hits, n, tmin, tmax, st);
-    }
+    RTW_DISPATCH(launch_intersect_t, sc, rays, hits, n, tmin, tmax);
 }
 
 }  // namespace rtw

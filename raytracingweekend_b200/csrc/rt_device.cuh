@@ -68,7 +68,48 @@ struct Rng {
 enum : uint32_t { SITE_MAIN = 0, SITE_BALL = 1, SITE_LENS = 1, SITE_MEDIUM0 = 2 };
 
 // ------------------------------------------------------------------------------------------------ loads
-RTW_DEV float4 ldg4(const float4* p) { return __ldg(p); }
+// SM = how much of the scene blob the block staged into shared memory: 0 nothing, 1 the hot sections, 2 all.
+// Staged sections are read with plain loads (ld.shared after address-space inference), the others through the
+// read-only global path in 16-byte vectors.
+template <bool STAGED, typename T>
+RTW_DEV T ld_pod(const T* p) {
+    static_assert(sizeof(T) % 4 == 0, "pod size");
+    if constexpr (STAGED) {
+        return *p;
+    } else if constexpr (sizeof(T) % 16 == 0) {
+        union {
+            T v;
+            float4 q[sizeof(T) / 16];
+        } u;
+#pragma unroll
+        for (int i = 0; i < (int)(sizeof(T) / 16); i++) u.q[i] = __ldg(reinterpret_cast<const float4*>(p) + i);
+        return u.v;
+    } else if constexpr (sizeof(T) == 8) {
+        union {
+            T v;
+            int2 q;
+        } u;
+        u.q = __ldg(reinterpret_cast<const int2*>(p));
+        return u.v;
+    } else {
+        union {
+            T v;
+            uint32_t q[sizeof(T) / 4];
+        } u;
+#pragma unroll
+        for (int i = 0; i < (int)(sizeof(T) / 4); i++) u.q[i] = __ldg(reinterpret_cast<const uint32_t*>(p) + i);
+        return u.v;
+    }
+}
+template <int SM, typename T>
+RTW_DEV T ld_hot(const T* p) { return ld_pod<(SM >= 1), T>(p); }
+template <int SM, typename T>
+RTW_DEV T ld_cold(const T* p) { return ld_pod<(SM >= 2), T>(p); }
+template <int SM>
+RTW_DEV int ld_u8(const uint8_t* p) {  // cold section bytes (Perlin permutations)
+    if constexpr (SM >= 2) return *p;
+    else return __ldg(p);
+}
 
 // ------------------------------------------------------------------------------------------------ transforms
 // translate/rotate_y chain composed on the host (hittable.h:299-311, 373-404): ray into object space.
@@ -88,10 +129,9 @@ RTW_DEV V3 xf_point_out(const DevXf& x, V3 p) {  // object -> world for points (
 // sphere_base::hit (sphere.h:46-81): near root, then far root, each with STRICT t_min < t < t_max (Q7).
 // FP32 form: the far-from-cancellation root comes from q = -b -/+ sqrt(disc), the other one from c/q, and the
 // discriminant from the perpendicular distance (|oc - (b/a) d|^2), which is what keeps r = 1000 usable.
-RTW_DEV bool sphere_roots(V3 oc, V3 d, float radius, float& t0, float& t1) {
-    float a = dot(d, d);
+// `a` = dot(d, d) and inv_a = 1/a are per-ray constants hoisted out of the primitive loop.
+RTW_DEV bool sphere_roots(V3 oc, V3 d, float a, float inv_a, float radius, float& t0, float& t1) {
     float b = dot(oc, d);
-    float inv_a = __frcp_rn(a);
     float ba = b * inv_a;
     V3 l = mk(fmaf(-ba, d.x, oc.x), fmaf(-ba, d.y, oc.y), fmaf(-ba, d.z, oc.z));
     float r2 = radius * radius;
@@ -137,22 +177,16 @@ RTW_DEV bool sphere_pick(float t0, float t1, float tmin, float tmax, float& t) {
 }
 
 // x?_rect::hit (hittable.h:149-165, 184-200, 241-257): INCLUSIVE bounds; a NaN t passes like the reference (Q39).
-// `ax` is the plane axis: 2 = xy_rect, 1 = xz_rect, 0 = yz_rect.
-RTW_DEV bool rect_hit(int type, float4 pa, float k, V3 o, V3 d, float tmin, float tmax, float& t_out) {
-    float on, dn, oa, da, ob, db;
-    if (type == RTW_PRIM_XY_RECT) {
-        on = o.z, dn = d.z, oa = o.x, da = d.x, ob = o.y, db = d.y;
-    } else if (type == RTW_PRIM_XZ_RECT) {
-        on = o.y, dn = d.y, oa = o.x, da = d.x, ob = o.z, db = d.z;
-    } else {
-        on = o.x, dn = d.x, oa = o.y, da = d.y, ob = o.z, db = d.z;
-    }
-    float t = __fdiv_rn(k - on, dn);
-    if (t < tmin || t > tmax) return false;
+// (on, dn) are the ray's origin/direction along the plane normal, (oa, da), (ob, db) along the two in-plane axes;
+// inv_n = 1/dn is shared by every rect of that orientation in the group.  (k - on) * inv_n is exactly 0 for a ray
+// that starts on the plane and +-inf / NaN for dn == 0 exactly as the division is.
+RTW_DEV bool rect_test(float4 ra, float k, float on, float inv_n, float oa, float da, float ob, float db, float tmin,
+                       float tmax, float& t_out) {
+    float t = (k - on) * inv_n;
     float a = fmaf(t, da, oa), b = fmaf(t, db, ob);
-    if (a < pa.x || a > pa.y || b < pa.z || b > pa.w) return false;
+    bool miss = (t < tmin) | (t > tmax) | (a < ra.x) | (a > ra.y) | (b < ra.z) | (b > ra.w);
     t_out = t;
-    return true;
+    return !miss;
 }
 
 // aabb::hit (aabb.h:17-47) with std::max/std::min written out so NaN behaves as in the reference (Q32).
@@ -190,55 +224,89 @@ struct HitId {
     int item;  // item that owns the hit (its xf applies)
 };
 
-// Test primitives [first, first+count) in list order (hittable_list.h:16-24): tmax shrinks to the running
-// closest hit — rects accept t == closest (a later object wins a tie), spheres need t < closest (Q38).
-// The second pass of hittable_list::hit (:26-34) re-selects the same winner for deterministic children.
-template <uint32_t F>
-RTW_DEV void test_prims(const DevScene& sc, int first, int count, V3 o, V3 d, float time, float tmin, float& t_best,
-                        int& prim_best) {
-    int cur_xf = 0;
-    V3 ol = o, dl = d;
-    for (int p = first; p < first + count; p++) {
-        uint32_t m = __ldg(&sc.pm[p]);
-        int type = m & PM_TYPE_MASK;
-        if (F & F_XF) {
-            int xf = (m >> PM_XF_SHIFT) & PM_XF_MASK;
-            if (xf != cur_xf) {
-                cur_xf = xf;
-                if (xf) {
-                    DevXf x = sc.xfs[xf - 1];
-                    xf_ray(x, o, d, ol, dl);
-                } else {
-                    ol = o, dl = d;
-                }
-            }
+// Per-ray constants of the primitive tests: reciprocal direction (rect planes, aabb slabs), a = d.d and 1/a (spheres).
+struct RayK {
+    V3 o, d, inv;
+    float a, inv_a;
+};
+RTW_DEV RayK make_rayk(V3 o, V3 d) {
+    RayK k;
+    k.o = o, k.d = d;
+    k.inv = mk(__frcp_rn(d.x), __frcp_rn(d.y), __frcp_rn(d.z));  // aabb.h:22 (1.0 / direction)
+    k.a = dot(d, d);
+    k.inv_a = __frcp_rn(k.a);
+    return k;
+}
+
+// hittable_list::hit (hittable_list.h:16-24) over groups [first, first+count): tmax shrinks to the running closest
+// hit — rects accept t == closest (a later object wins a tie), spheres need t < closest (Q38).  Inside a group the
+// records are ordered spheres, moving spheres, xy, xz, yz rects, each in list order, which evaluates the same
+// winner as the reference's interleaved order (see device_scene.hpp).  The second pass of hittable_list::hit
+// (:26-34) re-selects the same winner for deterministic children.
+// All loop bounds and record addresses are warp-uniform: one broadcast load per record.
+template <uint32_t F, int SM>
+RTW_DEV void test_groups(const SceneView& sv, int first, int count, const RayK& rk, float time, float tmin, float& t_best,
+                         int& prim_best) {
+    for (int gi = first; gi < first + count; gi++) {
+        DevGroup g = ld_hot<SM>(&sv.groups[gi]);
+        RayK k = rk;
+        if ((F & F_XF) && g.xf >= 0) {
+            DevXf x = ld_hot<SM>(&sv.xfs[g.xf]);
+            V3 ol, dl;
+            xf_ray(x, rk.o, rk.d, ol, dl);
+            k = make_rayk(ol, dl);
         }
-        float4 pa = ldg4(&sc.pa[p]);
-        float limit = t_best;
-        float t;
-        bool h;
-        if (type <= RTW_PRIM_MOVING_SPHERE) {
-            float t0, t1;
+        for (int r = g.sph0; r < g.sph1; r++) {
+            DevRec rec = ld_hot<SM>(&sv.recs[r]);
+            int id = __float_as_int(rec.b.w);
+            float t0, t1, t;
             bool roots;
-            if ((F & F_PRECISE) && (m & PM_PRECISE)) {
-                float4 pb = ldg4(&sc.pb[p]);
-                roots = sphere_roots_f64(ol, dl, sc.pd + 4 * __float_as_int(pb.w), t0, t1);
+            if ((F & F_PRECISE) && (id & REC_PRECISE)) {
+                roots = sphere_roots_f64(k.o, k.d, sv.pd + 4 * __float_as_int(rec.b.x), t0, t1);
+                id &= ~REC_PRECISE;
             } else {
-                V3 c = mk(pa.x, pa.y, pa.z);
-                if ((F & F_MOVING) && type == RTW_PRIM_MOVING_SPHERE) {
-                    float4 pb = ldg4(&sc.pb[p]);  // sphere.h:22-25 folded to c + time*delta on the host
-                    c = madd(c, time, mk(pb.x, pb.y, pb.z));
-                }
-                roots = sphere_roots(ol - c, dl, pa.w, t0, t1);
+                roots = sphere_roots(k.o - mk(rec.a.x, rec.a.y, rec.a.z), k.d, k.a, k.inv_a, rec.a.w, t0, t1);
             }
-            h = roots && sphere_pick(t0, t1, tmin, limit, t);
-        } else {
-            float4 pb = ldg4(&sc.pb[p]);
-            h = rect_hit(type, pa, pb.x, ol, dl, tmin, limit, t);
+            if (roots && sphere_pick(t0, t1, tmin, t_best, t)) {
+                t_best = t;
+                prim_best = id;
+            }
         }
-        if (h) {
-            t_best = t;
-            prim_best = p;
+        if (F & F_MOVING) {
+            for (int r = g.sph1; r < g.msph1; r++) {
+                DevRec rec = ld_hot<SM>(&sv.recs[r]);
+                // sphere.h:22-25 folded to c' + time*delta on the host
+                V3 c = madd(mk(rec.a.x, rec.a.y, rec.a.z), time, mk(rec.b.x, rec.b.y, rec.b.z));
+                float t0, t1, t;
+                if (sphere_roots(k.o - c, k.d, k.a, k.inv_a, rec.a.w, t0, t1) && sphere_pick(t0, t1, tmin, t_best, t)) {
+                    t_best = t;
+                    prim_best = __float_as_int(rec.b.w);
+                }
+            }
+        }
+        for (int r = g.msph1; r < g.xy1; r++) {  // xy_rect: plane z = k
+            DevRec rec = ld_hot<SM>(&sv.recs[r]);
+            float t;
+            if (rect_test(rec.a, rec.b.x, k.o.z, k.inv.z, k.o.x, k.d.x, k.o.y, k.d.y, tmin, t_best, t)) {
+                t_best = t;
+                prim_best = __float_as_int(rec.b.w);
+            }
+        }
+        for (int r = g.xy1; r < g.xz1; r++) {  // xz_rect: plane y = k
+            DevRec rec = ld_hot<SM>(&sv.recs[r]);
+            float t;
+            if (rect_test(rec.a, rec.b.x, k.o.y, k.inv.y, k.o.x, k.d.x, k.o.z, k.d.z, tmin, t_best, t)) {
+                t_best = t;
+                prim_best = __float_as_int(rec.b.w);
+            }
+        }
+        for (int r = g.xz1; r < g.yz1; r++) {  // yz_rect: plane x = k
+            DevRec rec = ld_hot<SM>(&sv.recs[r]);
+            float t;
+            if (rect_test(rec.a, rec.b.x, k.o.x, k.inv.x, k.o.y, k.d.y, k.o.z, k.d.z, tmin, t_best, t)) {
+                t_best = t;
+                prim_best = __float_as_int(rec.b.w);
+            }
         }
     }
 }

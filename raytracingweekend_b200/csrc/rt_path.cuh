@@ -10,11 +10,14 @@ namespace rtw {
 
 // Returns true when the path continues with the new `ray`/`beta`; false when it ended (L updated).
 // `bounce` is the 1-based index of this color() invocation (Philox counter word).
-template <uint32_t F>
-RTW_DEV bool path_step(const DevScene& sc, const Rng& rng, uint32_t bounce, Ray& ray, V3& beta, V3& L, int* stack,
-                       int stride) {
+template <uint32_t F, int SM>
+RTW_DEV bool path_step(const DevScene& sc, const SceneView& sv, const Rng& rng, uint32_t bounce, Ray& ray, V3& beta, V3& L,
+                       int* stack, int stride) {
     // :52 world.hit(r, 0.001f, DBL_MAX, rec)
-    HitId h = closest_hit<F, false>(sc, ray.o, ray.d, ray.time, 0.001f, FLT_MAX, &rng, bounce, stack, stride);
+    HitId h = closest_hit<F, SM, false>(sc, sv, ray.o, ray.d, ray.time, 0.001f, FLT_MAX, &rng, bounce, stack, stride);
+    // The bounce's main uniforms are drawn here, before control flow diverges by material: every lane of the
+    // warp runs the ten Philox rounds together instead of once per material branch.
+    U4 rmain = rng.draw(bounce, SITE_MAIN);
     if (h.prim == -1) {  // :141-159
         L = L + beta * background(sc, ray.d);
         return false;
@@ -22,13 +25,13 @@ RTW_DEV bool path_step(const DevScene& sc, const Rng& rng, uint32_t bounce, Ray&
     int mat_idx;
     {
         // material first: whether u,v are needed depends on its texture
-        if (h.prim < 0) mat_idx = sc.items[-2 - h.prim].material;
-        else mat_idx = (int)(__ldg(&sc.pm[h.prim]) >> PM_MAT_SHIFT);
+        if (h.prim < 0) mat_idx = ld_hot<SM>(&sv.items[-2 - h.prim].material);
+        else mat_idx = (int)(ld_cold<SM>(&sv.pm[h.prim]) >> PM_MAT_SHIFT);
     }
-    DevMat m = sc.mats[mat_idx];
+    DevMat m = ld_cold<SM>(&sv.mats[mat_idx]);
     bool need_uv = (F & F_TEXTURES) && !m.tex_is_constant &&
                    (m.type == RTW_MAT_LAMBERTIAN || m.type == RTW_MAT_DIFFUSE_LIGHT || m.type == RTW_MAT_ISOTROPIC);
-    HitRec rec = complete_hit<F>(sc, h, ray.o, ray.d, ray.time, need_uv);
+    HitRec rec = complete_hit<F, SM>(sv, h, ray.o, ray.d, ray.time, need_uv);
 
     if (sc.render_type == RTW_RENDER_NORMAL) {  // :135-136
         L = L + beta * (0.5f * (rec.n + mk(1.0f, 1.0f, 1.0f)));
@@ -37,7 +40,7 @@ RTW_DEV bool path_step(const DevScene& sc, const Rng& rng, uint32_t bounce, Ray&
 
     switch (m.type) {
         case RTW_MAT_DIFFUSE_LIGHT: {  // material.h:232-244: no scatter; one-sided emission (Q23)
-            if (dot(rec.n, ray.d) > 0.0f) L = L + beta * material_texture(sc, m, rec.u, rec.v, rec.p);
+            if (dot(rec.n, ray.d) > 0.0f) L = L + beta * material_texture<SM>(sv, m, rec.u, rec.v, rec.p);
             return false;  // :62-63
         }
         case RTW_MAT_METAL: {  // material.h:128-136 -> specular branch :114-115
@@ -83,34 +86,34 @@ RTW_DEV bool path_step(const DevScene& sc, const Rng& rng, uint32_t bounce, Ray&
                 float om2 = om * om;
                 reflect_prob = r0 + (1.0f - r0) * (om2 * om2 * om);
             }
-            float u = rng.draw(bounce, SITE_MAIN).x;  // :209-212 (drawn even on total internal reflection)
+            float u = rmain.x;  // :209-212 (drawn even on total internal reflection)
             ray.o = rec.p;
             ray.d = (u < reflect_prob) ? reflected : refracted;
             return true;  // attenuation (1,1,1)
         }
         case RTW_MAT_ISOTROPIC: {  // material.h:257-262
             U4 b = rng.draw(bounce, SITE_BALL);
-            beta = beta * material_texture(sc, m, rec.u, rec.v, rec.p);
+            beta = beta * material_texture<SM>(sv, m, rec.u, rec.v, rec.p);
             ray.o = rec.p;
             ray.d = random_in_unit_ball(b.x, b.y, b.z);
             return true;
         }
         default: {  // lambertian: material.h:81-119 + mixture importance sampling :117-132
-            V3 att = material_texture(sc, m, rec.u, rec.v, rec.p);
-            U4 r = rng.draw(bounce, SITE_MAIN);
+            V3 att = material_texture<SM>(sv, m, rec.u, rec.v, rec.p);
+            U4 r = rmain;
             Onb uvw = onb_from_w(rec.n);  // cosine_pdf ctor (pdf.h:18)
             bool have_lights = sc.n_lights > 0;  // :118
             V3 dir;
             if (!have_lights || r.x < 0.5f) {  // mixture_pdf::generate (pdf.h:69-75): p[0] = cosine
                 dir = onb_local(uvw, random_cosine_direction(r.z, r.w));
             } else {
-                dir = lights_random(sc, rec.p, r.y, r.z, r.w);
+                dir = lights_random<SM>(sc, sv, rec.p, r.y, r.z, r.w);
             }
             V3 nd = normalize(dir);
             float cos_w = dot(nd, uvw.w);
             float pdf_cos = (cos_w <= 0.0f) ? 0.0f : cos_w / kPi;  // cosine_pdf::value (pdf.h:20-24)
             float pdf_val = pdf_cos;
-            if (have_lights) pdf_val = 0.5f * pdf_cos + 0.5f * lights_pdf(sc, rec.p, dir);  // pdf.h:64-67
+            if (have_lights) pdf_val = 0.5f * pdf_cos + 0.5f * lights_pdf<SM>(sc, sv, rec.p, dir);  // pdf.h:64-67
             if (pdf_val <= 0.0f) return false;  // :126-127 (emitted is zero for a lambertian)
             float cos_n = dot(rec.n, nd);
             float spdf = (cos_n < 0.0f) ? 0.0f : cos_n / kPi;  // lambertian::scattering_pdf (material.h:115-119)

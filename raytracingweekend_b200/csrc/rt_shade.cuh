@@ -9,28 +9,29 @@ constexpr float kPi = 3.14159265358979323846f;
 // ------------------------------------------------------------------------------------------------ Perlin
 // perlin::noise (noise.h:89-151, InterpolationType::PERLIN) + perlin_interp (noise.h:40-60) with the Hermite
 // cubic `smooth` (noise.h:9-12, :19).
-RTW_DEV float perlin_noise(const DevScene& sc, V3 p) {
+template <int SM>
+RTW_DEV float perlin_noise(const SceneView& sv, V3 p) {
     float fx = floorf(p.x), fy = floorf(p.y), fz = floorf(p.z);
     float u = p.x - fx, v = p.y - fy, w = p.z - fz;
     int i = (int)fx, j = (int)fy, k = (int)fz;
     float uu = u * u * (3.0f - 2.0f * u), vv = v * v * (3.0f - 2.0f * v), ww = w * w * (3.0f - 2.0f * w);
-    const uint8_t* px = sc.perlin_perm;
-    const uint8_t* py = sc.perlin_perm + 256;
-    const uint8_t* pz = sc.perlin_perm + 512;
+    const uint8_t* px = sv.perlin_perm;
+    const uint8_t* py = sv.perlin_perm + 256;
+    const uint8_t* pz = sv.perlin_perm + 512;
     float accum = 0.0f;
 #pragma unroll
     for (int di = 0; di < 2; di++) {
-        int hx = __ldg(&px[(i + di) & 255]);
+        int hx = ld_u8<SM>(&px[(i + di) & 255]);
         float wi = di ? uu : 1.0f - uu;
 #pragma unroll
         for (int dj = 0; dj < 2; dj++) {
-            int hy = __ldg(&py[(j + dj) & 255]);
+            int hy = ld_u8<SM>(&py[(j + dj) & 255]);
             float wj = dj ? vv : 1.0f - vv;
 #pragma unroll
             for (int dk = 0; dk < 2; dk++) {
-                int hz = __ldg(&pz[(k + dk) & 255]);
+                int hz = ld_u8<SM>(&pz[(k + dk) & 255]);
                 float wk = dk ? ww : 1.0f - ww;
-                float4 c = ldg4(&sc.perlin_ranvec[hx ^ hy ^ hz]);
+                float4 c = ld_cold<SM>(&sv.perlin_ranvec[hx ^ hy ^ hz]);
                 float dp = fmaf(c.x, u - di, fmaf(c.y, v - dj, c.z * (w - dk)));
                 accum = fmaf(wi * wj * wk, dp, accum);
             }
@@ -38,10 +39,11 @@ RTW_DEV float perlin_noise(const DevScene& sc, V3 p) {
     }
     return accum;
 }
-RTW_DEV float perlin_turb(const DevScene& sc, V3 p) {  // noise.h:74-86, depth 7
+template <int SM>
+RTW_DEV float perlin_turb(const SceneView& sv, V3 p) {  // noise.h:74-86, depth 7
     float accum = 0.0f, weight = 1.0f;
     for (int i = 0; i < 7; i++) {
-        accum = fmaf(weight, perlin_noise(sc, p), accum);
+        accum = fmaf(weight, perlin_noise<SM>(sv, p), accum);
         weight *= 0.5f;
         p = p * 2.0f;
     }
@@ -49,9 +51,10 @@ RTW_DEV float perlin_turb(const DevScene& sc, V3 p) {  // noise.h:74-86, depth 7
 }
 
 // texture::value(u, v, p) (texture.h:21-24, 35-46, 57-68, 81-94)
-RTW_DEV V3 texture_value(const DevScene& sc, int tex, float u, float v, V3 p) {
+template <int SM>
+RTW_DEV V3 texture_value(const SceneView& sv, int tex, float u, float v, V3 p) {
     for (int guard = 0; guard < 16; guard++) {
-        DevTex t = sc.texs[tex];
+        DevTex t = ld_cold<SM>(&sv.texs[tex]);
         if (t.type == RTW_TEX_CONSTANT) return mk(t.r, t.g, t.b);
         if (t.type == RTW_TEX_CHECKER) {
             float sines = sinf(10.0f * p.x) * sinf(10.0f * p.y) * sinf(10.0f * p.z);
@@ -59,7 +62,7 @@ RTW_DEV V3 texture_value(const DevScene& sc, int tex, float u, float v, V3 p) {
             continue;
         }
         if (t.type == RTW_TEX_NOISE) {
-            float g = 0.5f * (1.0f + sinf(fmaf(t.scale, p.z, 10.0f * perlin_turb(sc, p))));
+            float g = 0.5f * (1.0f + sinf(fmaf(t.scale, p.z, 10.0f * perlin_turb<SM>(sv, p))));
             return mk(g, g, g);
         }
         // image_texture (texture.h:81-94): nearest texel, v flipped
@@ -67,15 +70,16 @@ RTW_DEV V3 texture_value(const DevScene& sc, int tex, float u, float v, V3 p) {
         int j = (int)((1.0f - v) * t.ny - 0.001f);
         i = max(min(i, t.nx - 1), 0);
         j = max(min(j, t.ny - 1), 0);
-        const uint8_t* px = sc.texels + t.image_offset + 3 * i + 3 * t.nx * j;
+        const uint8_t* px = sv.texels + t.image_offset + 3 * i + 3 * t.nx * j;
         return mk(__ldg(px) / 255.0f, __ldg(px + 1) / 255.0f, __ldg(px + 2) / 255.0f);
     }
     return mk(0.0f, 0.0f, 0.0f);
 }
 
-RTW_DEV V3 material_texture(const DevScene& sc, const DevMat& m, float u, float v, V3 p) {
+template <int SM>
+RTW_DEV V3 material_texture(const SceneView& sv, const DevMat& m, float u, float v, V3 p) {
     if (m.tex_is_constant) return mk(m.r, m.g, m.b);
-    return texture_value(sc, m.texture, u, v, p);
+    return texture_value<SM>(sv, m.texture, u, v, p);
 }
 
 // ------------------------------------------------------------------------------------------------ sampling
@@ -137,18 +141,20 @@ RTW_DEV float light_rect_pdf(const DevLight& l, V3 o, V3 v) {
 RTW_DEV float light_sphere_pdf(const DevLight& l, V3 o, V3 v) {
     V3 c = mk(l.a0, l.a1, l.a2);
     float t0, t1, t;
-    if (!sphere_roots(o - c, v, l.a3, t0, t1) || !sphere_pick(t0, t1, 0.001f, INFINITY, t)) return 0.0f;
+    float a = dot(v, v);
+    if (!sphere_roots(o - c, v, a, __frcp_rn(a), l.a3, t0, t1) || !sphere_pick(t0, t1, 0.001f, INFINITY, t)) return 0.0f;
     V3 co = c - o;
     float q = l.a3 * l.a3 / dot(co, co);
     float one_minus_cmax = q / (1.0f + sqrtf(1.0f - q));  // NaN when the origin is inside, like the reference (Q17)
     return 1.0f / (2.0f * kPi * one_minus_cmax);
 }
 // hittable_list::pdf_value (hittable_list.h:44-53)
-RTW_DEV float lights_pdf(const DevScene& sc, V3 o, V3 v) {
+template <int SM>
+RTW_DEV float lights_pdf(const DevScene& sc, const SceneView& sv, V3 o, V3 v) {
     float weight = 1.0f / (float)sc.n_lights;
     float sum = 0.0f;
     for (int i = 0; i < sc.n_lights; i++) {
-        DevLight l = sc.lights[i];
+        DevLight l = ld_hot<SM>(&sv.lights[i]);
         float pv = 0.0f;  // hittable.h:36 default
         if (l.type == RTW_LIGHT_XZ_RECT) pv = light_rect_pdf(l, o, v);
         else if (l.type == RTW_LIGHT_SPHERE) pv = light_sphere_pdf(l, o, v);
@@ -158,10 +164,11 @@ RTW_DEV float lights_pdf(const DevScene& sc, V3 o, V3 v) {
 }
 // hittable_list::random (hittable_list.h:55-59) -> xz_rect::random (hittable.h:224-228) |
 // sphere_base::random (sphere.h:101-108) | hittable::random default (hittable.h:37)
-RTW_DEV V3 lights_random(const DevScene& sc, V3 o, float upick, float r1, float r2) {
+template <int SM>
+RTW_DEV V3 lights_random(const DevScene& sc, const SceneView& sv, V3 o, float upick, float r1, float r2) {
     int n = sc.n_lights;
     int idx = min(n - 1, (int)((float)n * upick));  // utility.h:22-25 with a = 0, b = n-1
-    DevLight l = sc.lights[idx];
+    DevLight l = ld_hot<SM>(&sv.lights[idx]);
     if (l.type == RTW_LIGHT_XZ_RECT) {
         V3 pt = mk(fmaf(l.a1 - l.a0, r1, l.a0), l.k, fmaf(l.a3 - l.a2, r2, l.a2));
         return pt - o;
