@@ -172,9 +172,10 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
 
     // primitive-test groups and records (device_scene.hpp): split a run of primitives into maximal runs that
     // share a transform chain, and order each run's records spheres, moving spheres, xy, xz, yz rects.
+    // Built with INDICES first; converted to blob byte offsets once the section offsets are known (below).
     std::vector<DevGroup> groups;
     std::vector<DevRec> recs;
-    auto add_groups = [&](int first, int count, int& first_group, int& n_groups) {
+    auto add_groups = [&](int first, int count, int& first_group, int& end_group) {
         first_group = (int)groups.size();
         int i = first;
         while (i < first + count) {
@@ -194,7 +195,7 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
                         int id = p;
                         if (pm[p] & PM_PRECISE) {
                             id |= REC_PRECISE;
-                            r.b.x = pb[p].w;  // pd index bits
+                            r.b.x = pb[p].w;  // pd index bits (-> byte offset below)
                         }
                         r.b.w = __int_as_float_host(id);
                     } else if (k == 1) {
@@ -209,7 +210,7 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
             groups.push_back(g);
             i = j;
         }
-        n_groups = (int)groups.size() - first_group;
+        end_group = (int)groups.size();
     };
 
     std::vector<DevItem> items(fs->n_items);
@@ -217,7 +218,7 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
     for (int i = 0; i < fs->n_items; i++) {
         const rtw_flat_item& it = fs->items[i];
         DevItem d{};
-        d.type = it.type, d.xf = it.xf, d.first = it.first, d.count = it.count;
+        d.type = it.type, d.xf = it.xf, d.first = it.first, d.end = it.first + it.count;
         d.material = it.material, d.flip = it.flip;
         d.density_eff = (float)(it.density * (it.multiplicity > 0 ? it.multiplicity : 1));
         if (it.type == RTW_ITEM_BVH) {
@@ -225,7 +226,7 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
             int dep = bvh_depth(fs, it.first, 0);
             if (dep > max_depth) max_depth = dep;
         } else {
-            add_groups(it.first, it.count, d.first, d.count);
+            add_groups(it.first, it.count, d.first, d.end);
         }
         if (it.type == RTW_ITEM_MEDIUM) feat |= F_MEDIA;
         items[i] = d;
@@ -235,11 +236,11 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
         return nullptr;
     }
 
-    std::vector<float4> node_lo(fs->n_nodes), node_hi(fs->n_nodes);
+    std::vector<DevNode> nodes(fs->n_nodes);
     for (int i = 0; i < fs->n_nodes; i++) {
         const rtw_flat_node& n = fs->nodes[i];
-        node_lo[i] = make_float4((float)n.bmin[0], (float)n.bmin[1], (float)n.bmin[2], __int_as_float_host(n.left));
-        node_hi[i] = make_float4((float)n.bmax[0], (float)n.bmax[1], (float)n.bmax[2], __int_as_float_host(n.right));
+        nodes[i].lo = make_float4((float)n.bmin[0], (float)n.bmin[1], (float)n.bmin[2], __int_as_float_host(n.left));
+        nodes[i].hi = make_float4((float)n.bmax[0], (float)n.bmax[1], (float)n.bmax[2], __int_as_float_host(n.right));
     }
     std::vector<int2> leaves(fs->n_leaves);
     for (int i = 0; i < fs->n_leaves; i++) add_groups(fs->leaves[i].first_prim, fs->leaves[i].prim_count, leaves[i].x, leaves[i].y);
@@ -295,33 +296,66 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
     std::vector<uint8_t> texels;
     if (fs->n_texel_bytes) texels.assign(fs->texels, fs->texels + fs->n_texel_bytes);
 
-    // pack the blob: 16-byte aligned sections, hot first
-    std::vector<uint8_t> blob;
+    // blob layout: 16-byte aligned sections, hot first; offsets first (the records hold byte offsets), then the bytes
+    const size_t sec_bytes[SEC_COUNT] = {
+        items.size() * sizeof(DevItem), groups.size() * sizeof(DevGroup), recs.size() * sizeof(DevRec), xfs.size() * sizeof(DevXf),
+        lights.size() * sizeof(DevLight), nodes.size() * sizeof(DevNode), leaves.size() * sizeof(int2),
+        pm.size() * sizeof(uint32_t), pa.size() * sizeof(float4), pb.size() * sizeof(float4), pd.size() * sizeof(double),
+        mats.size() * sizeof(DevMat), texs.size() * sizeof(DevTex), ranvec.size() * sizeof(float4), perm.size()};
     uint32_t off[SEC_COUNT] = {};
-    auto put = [&](int sec, const void* data, size_t bytes) {
-        off[sec] = (uint32_t)blob.size();
-        const uint8_t* p = (const uint8_t*)data;
-        if (bytes) blob.insert(blob.end(), p, p + bytes);
-        blob.resize((blob.size() + 15) & ~(size_t)15, 0);
+    uint32_t hot_bytes = 0;
+    size_t total = 0;
+    for (int k = 0; k < SEC_COUNT; k++) {
+        off[k] = (uint32_t)total;
+        total = (total + sec_bytes[k] + 15) & ~(size_t)15;
+        if (k == SEC_LEAVES) hot_bytes = (uint32_t)total;
+    }
+    if (total == 0) total = 16;
+    if (total > 0x7fffffffu) {
+        set_error("scene_create: scene too large for 31-bit blob offsets");
+        return nullptr;
+    }
+    // indices -> byte offsets
+    auto xf_off = [&](int idx) { return idx < 0 ? -1 : (int32_t)(off[SEC_XFS] + (uint32_t)idx * sizeof(DevXf)); };
+    auto rec_off = [&](int idx) { return (int32_t)(off[SEC_RECS] + (uint32_t)idx * sizeof(DevRec)); };
+    auto group_off = [&](int idx) { return (int32_t)(off[SEC_GROUPS] + (uint32_t)idx * sizeof(DevGroup)); };
+    auto ref_off = [&](int ref) {
+        return ref >= 0 ? (int32_t)(off[SEC_NODES] + (uint32_t)ref * sizeof(DevNode)) : ~(int32_t)(off[SEC_LEAVES] + (uint32_t)(~ref) * sizeof(int2));
     };
-    put(SEC_ITEMS, items.data(), items.size() * sizeof(DevItem));
-    put(SEC_GROUPS, groups.data(), groups.size() * sizeof(DevGroup));
-    put(SEC_RECS, recs.data(), recs.size() * sizeof(DevRec));
-    put(SEC_XFS, xfs.data(), xfs.size() * sizeof(DevXf));
-    put(SEC_LIGHTS, lights.data(), lights.size() * sizeof(DevLight));
-    put(SEC_NODE_LO, node_lo.data(), node_lo.size() * sizeof(float4));
-    put(SEC_NODE_HI, node_hi.data(), node_hi.size() * sizeof(float4));
-    put(SEC_LEAVES, leaves.data(), leaves.size() * sizeof(int2));
-    uint32_t hot_bytes = (uint32_t)blob.size();
-    put(SEC_PM, pm.data(), pm.size() * sizeof(uint32_t));
-    put(SEC_PA, pa.data(), pa.size() * sizeof(float4));
-    put(SEC_PB, pb.data(), pb.size() * sizeof(float4));
-    put(SEC_PD, pd.data(), pd.size() * sizeof(double));
-    put(SEC_MATS, mats.data(), mats.size() * sizeof(DevMat));
-    put(SEC_TEXS, texs.data(), texs.size() * sizeof(DevTex));
-    put(SEC_RANVEC, ranvec.data(), ranvec.size() * sizeof(float4));
-    put(SEC_PERM, perm.data(), perm.size());
-    if (blob.empty()) blob.resize(16, 0);
+    for (DevGroup& g : groups) {
+        g.xf = xf_off(g.xf);
+        g.sph0 = rec_off(g.sph0), g.sph1 = rec_off(g.sph1), g.msph1 = rec_off(g.msph1);
+        g.xy1 = rec_off(g.xy1), g.xz1 = rec_off(g.xz1), g.yz1 = rec_off(g.yz1);
+    }
+    for (DevItem& d : items) {
+        d.xf = xf_off(d.xf);
+        if (d.type == RTW_ITEM_BVH) d.first = ref_off(d.first), d.end = 0;
+        else d.first = group_off(d.first), d.end = group_off(d.end);
+    }
+    for (DevNode& n : nodes) {
+        int l, r;
+        memcpy(&l, &n.lo.w, 4), memcpy(&r, &n.hi.w, 4);
+        n.lo.w = __int_as_float_host(ref_off(l)), n.hi.w = __int_as_float_host(ref_off(r));
+    }
+    for (int2& lf : leaves) lf.x = group_off(lf.x), lf.y = group_off(lf.y);
+    auto pd_off = [&](float idx_bits) {
+        int idx;
+        memcpy(&idx, &idx_bits, 4);
+        return __int_as_float_host((int32_t)(off[SEC_PD] + (uint32_t)idx * 4u * sizeof(double)));
+    };
+    for (int i = 0; i < fs->n_prims; i++)
+        if (pm[i] & PM_PRECISE) pb[i].w = pd_off(pb[i].w);
+    for (DevRec& r : recs) {
+        int id;
+        memcpy(&id, &r.b.w, 4);
+        if (id & REC_PRECISE) r.b.x = pd_off(r.b.x);
+    }
+
+    std::vector<uint8_t> blob(total, 0);
+    const void* sec_data[SEC_COUNT] = {items.data(), groups.data(), recs.data(), xfs.data(), lights.data(), nodes.data(), leaves.data(),
+                                       pm.data(), pa.data(), pb.data(), pd.data(), mats.data(), texs.data(), ranvec.data(), perm.data()};
+    for (int k = 0; k < SEC_COUNT; k++)
+        if (sec_bytes[k]) memcpy(blob.data() + off[k], sec_data[k], sec_bytes[k]);
 
     rtw_scene* s = new (std::nothrow) rtw_scene();
     if (!s) return nullptr;

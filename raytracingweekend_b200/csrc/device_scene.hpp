@@ -2,12 +2,16 @@
 //
 // The whole scene except image texels is ONE packed blob of 16-byte aligned sections, ordered hot-first:
 //
-//   [ items | groups | recs | xfs | lights | node_lo | node_hi | leaves ]   <- "hot": touched per primitive test
+//   [ items | groups | recs | xfs | lights | nodes | leaves ]               <- "hot": touched per primitive test
 //   [ pm | pa | pb | pd | mats | texs | perlin_ranvec | perlin_perm ]       <- "cold": touched once per ray
 //
 // A render block stages a prefix of the blob into shared memory (everything, the hot part, or nothing,
-// depending on its size) and walks it with warp-uniform indices, so every primitive-test load is a shared
+// depending on its size) and walks it with warp-uniform addresses, so every primitive-test load is a shared
 // memory broadcast; larger scenes read the same sections from global memory through L1 (ld.global.nc).
+//
+// Everything inside the blob is addressed by BYTE OFFSET FROM THE BLOB START (uint32): the same offset is
+// valid against the shared-memory copy (32-bit shared address = staged base + offset, `ld.shared.v4`) and against
+// the global copy (`ld.global.nc.v4`), and the inner loops advance one address register by 32 bytes per record.
 //
 // Primitive tests are driven by `DevGroup`s: a group is a run of primitives of one item that share a
 // transform chain, re-ordered by kind (spheres, moving spheres, xy/xz/yz rects) so the inner loops are
@@ -36,16 +40,20 @@ struct DevXf {
 };
 
 struct DevItem {
-    int32_t type, xf, first, count;  // xf: index into xfs or -1; PRIMS/MEDIUM: first/count are GROUPS; BVH: first = root node
+    int32_t type;     // RTW_ITEM_*
+    int32_t xf;       // byte offset of the item's DevXf, or -1
+    int32_t first;    // PRIMS/MEDIUM: byte offset of the first DevGroup; BVH: root reference (see DevNode)
+    int32_t end;      // PRIMS/MEDIUM: byte offset one past the last DevGroup
     int32_t material, flip;
     float density_eff;  // density * multiplicity
     float pad;
 };
 
-// Run of primitive-test records sharing one transform chain (xf = index into xfs, or -1).
-// recs[sph0, sph1) spheres; [sph1, msph1) moving spheres; [msph1, xy1) xy_rects; [xy1, xz1) xz_rects; [xz1, yz1) yz_rects.
+// Run of primitive-test records sharing one transform chain.  All members are byte offsets into the blob:
+// [sph0, sph1) spheres; [sph1, msph1) moving spheres; [msph1, xy1) xy_rects; [xy1, xz1) xz_rects; [xz1, yz1) yz_rects.
 struct DevGroup {
-    int32_t xf, sph0, sph1, msph1;
+    int32_t xf;  // byte offset of the DevXf, or -1
+    int32_t sph0, sph1, msph1;
     int32_t xy1, xz1, yz1, pad;
 };
 
@@ -57,6 +65,13 @@ struct DevRec {
     float4 a, b;
 };
 constexpr int32_t REC_PRECISE = 1 << 30;
+
+// bvh_node (hittable.h:137-139), 32 bytes.  Child references: >= 0 byte offset of a DevNode; < 0: ~(byte offset of
+// the leaf's int2 {first group offset, end group offset}).
+struct DevNode {
+    float4 lo;  // bmin.xyz, left reference (int bits)
+    float4 hi;  // bmax.xyz, right reference (int bits)
+};
 
 struct DevMat {
     float r, g, b, param;  // metal: albedo + fuzz; dielectric: param = ref_idx; textured: resolved constant colour
@@ -91,8 +106,8 @@ enum : uint32_t {  // feature mask -> kernel specialisation
 };
 
 enum {  // blob sections, in blob order
-    SEC_ITEMS = 0, SEC_GROUPS, SEC_RECS, SEC_XFS, SEC_LIGHTS, SEC_NODE_LO, SEC_NODE_HI, SEC_LEAVES,  // hot
-    SEC_PM, SEC_PA, SEC_PB, SEC_PD, SEC_MATS, SEC_TEXS, SEC_RANVEC, SEC_PERM,                       // cold
+    SEC_ITEMS = 0, SEC_GROUPS, SEC_RECS, SEC_XFS, SEC_LIGHTS, SEC_NODES, SEC_LEAVES,  // hot
+    SEC_PM, SEC_PA, SEC_PB, SEC_PD, SEC_MATS, SEC_TEXS, SEC_RANVEC, SEC_PERM,        // cold
     SEC_COUNT
 };
 
@@ -114,24 +129,10 @@ struct DevRenderParams {
     uint32_t seed_lo, seed_hi;
 };
 
-// Typed view of the blob: pointers into shared memory for the staged prefix, into global memory otherwise.
+// Where the blob lives for this block: `sbase` = 32-bit shared address of the staged prefix, `g` = global copy.
 struct SceneView {
-    const DevItem* items;
-    const DevGroup* groups;
-    const DevRec* recs;
-    const DevXf* xfs;
-    const DevLight* lights;
-    const float4* node_lo;  // bmin.xyz, left (int bits)
-    const float4* node_hi;  // bmax.xyz, right (int bits)
-    const int2* leaves;     // (first group, group count)
-    const uint32_t* pm;
-    const float4* pa;
-    const float4* pb;
-    const double* pd;  // 4 doubles per precise sphere (cx cy cz r)
-    const DevMat* mats;
-    const DevTex* texs;
-    const float4* perlin_ranvec;
-    const uint8_t* perlin_perm;  // 3*256
+    uint32_t sbase;
+    const uint8_t* g;
     const uint8_t* texels;
 };
 

@@ -17,7 +17,10 @@ constexpr int kBlock = 128;   // 4 warps
 constexpr int kTileW = 16;    // block tile: 16 x 8 pixels, warp tile 8 x 4
 constexpr int kTileH = 8;
 
-// Stage the first `bytes` of the scene blob into shared memory (16-byte vectors, whole block) and build the typed view.
+// Stage a prefix of the scene blob into shared memory (16-byte vectors, whole block) and return the view.
+// `sbase` is laundered through an empty volatile asm after the barrier: every staged load depends on it, so none can
+// be scheduled above the barrier, and the compiler keeps it in a register instead of re-deriving the shared window
+// address at each use.
 template <int SM>
 RTW_DEV SceneView stage_scene(const DevScene& sc, uint4* smem) {
     const uint32_t staged = SM == 2 ? sc.all_bytes : (SM == 1 ? sc.hot_bytes : 0u);
@@ -26,28 +29,10 @@ RTW_DEV SceneView stage_scene(const DevScene& sc, uint4* smem) {
         for (uint32_t i = threadIdx.x; i < staged / 16; i += blockDim.x) smem[i] = __ldg(src + i);
         __syncthreads();
     }
-    const uint8_t* sm = reinterpret_cast<const uint8_t*>(smem);
-    const uint8_t* gm = sc.blob;
     SceneView v;
-#define RTW_SEC(field, type, sec, hot) \
-    v.field = reinterpret_cast<const type*>(((SM == 2) || (SM == 1 && hot)) ? sm + sc.off[sec] : gm + sc.off[sec]);
-    RTW_SEC(items, DevItem, SEC_ITEMS, true)
-    RTW_SEC(groups, DevGroup, SEC_GROUPS, true)
-    RTW_SEC(recs, DevRec, SEC_RECS, true)
-    RTW_SEC(xfs, DevXf, SEC_XFS, true)
-    RTW_SEC(lights, DevLight, SEC_LIGHTS, true)
-    RTW_SEC(node_lo, float4, SEC_NODE_LO, true)
-    RTW_SEC(node_hi, float4, SEC_NODE_HI, true)
-    RTW_SEC(leaves, int2, SEC_LEAVES, true)
-    RTW_SEC(pm, uint32_t, SEC_PM, false)
-    RTW_SEC(pa, float4, SEC_PA, false)
-    RTW_SEC(pb, float4, SEC_PB, false)
-    RTW_SEC(pd, double, SEC_PD, false)
-    RTW_SEC(mats, DevMat, SEC_MATS, false)
-    RTW_SEC(texs, DevTex, SEC_TEXS, false)
-    RTW_SEC(perlin_ranvec, float4, SEC_RANVEC, false)
-    RTW_SEC(perlin_perm, uint8_t, SEC_PERM, false)
-#undef RTW_SEC
+    v.sbase = (uint32_t)__cvta_generic_to_shared(smem);
+    asm volatile("" : "+r"(v.sbase)::"memory");
+    v.g = sc.blob;
     v.texels = sc.texels;
     return v;
 }
@@ -142,7 +127,9 @@ __global__ void __launch_bounds__(kBlock) intersect_kernel(const __grid_constant
         out.prim = -1, out.material = -1;
         out.t = out.u = out.v = out.nx = out.ny = out.nz = 0.0f;
     } else {
-        HitRec rec = complete_hit<F, SM>(sv, h, o, d, r.time, true);
+        uint32_t pm;
+        (void)hit_material<SM>(sc, sv, h, pm);
+        HitRec rec = complete_hit<F, SM>(sc, sv, h, pm, o, d, r.time, true);
         out.prim = h.prim, out.material = rec.mat;
         out.t = h.t, out.u = rec.u, out.v = rec.v;
         out.nx = rec.n.x, out.ny = rec.n.y, out.nz = rec.n.z;

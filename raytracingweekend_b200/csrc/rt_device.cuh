@@ -32,6 +32,15 @@ RTW_DEV V3 normalize(V3 a) {  // vec3.h:61-67
     return a * inv;
 }
 RTW_DEV V3 madd(V3 o, float t, V3 d) { return mk(fmaf(t, d.x, o.x), fmaf(t, d.y, o.y), fmaf(t, d.z, o.z)); }
+RTW_DEV V3 sel(bool c, V3 a, V3 b) { return mk(c ? a.x : b.x, c ? a.y : b.y, c ? a.z : b.z); }
+
+// 1/x as a single MUFU.RCP (1 ulp; 1/0 = inf, 1/denormal = inf under ftz — the slab and plane tests only need the
+// IEEE special values, not correct rounding; tier-2 tolerance is 1e-5 relative).
+RTW_DEV float rcp_fast(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
 
 struct Ray {  // ray.h:17-20 — direction is NOT normalised
     V3 o, d;
@@ -69,46 +78,105 @@ enum : uint32_t { SITE_MAIN = 0, SITE_BALL = 1, SITE_LENS = 1, SITE_MEDIUM0 = 2 
 
 // ------------------------------------------------------------------------------------------------ loads
 // SM = how much of the scene blob the block staged into shared memory: 0 nothing, 1 the hot sections, 2 all.
-// Staged sections are read with plain loads (ld.shared after address-space inference), the others through the
-// read-only global path in 16-byte vectors.
-template <bool STAGED, typename T>
-RTW_DEV T ld_pod(const T* p) {
-    static_assert(sizeof(T) % 4 == 0, "pod size");
+// `off` is a byte offset from the blob start (device_scene.hpp).  Staged data is read with explicit ld.shared on a
+// 32-bit address (one LDS per 16 bytes, no generic-address arithmetic), the rest through the read-only global path.
+// The asm is not volatile on purpose: the blob is immutable once staged, so loads may be scheduled freely; they
+// depend on `sbase`, which is produced after the staging barrier (stage_scene), and cannot move above it.
+template <bool STAGED>
+RTW_DEV float4 ldb4(const SceneView& sv, uint32_t off) {
+    float4 v;
     if constexpr (STAGED) {
-        return *p;
-    } else if constexpr (sizeof(T) % 16 == 0) {
-        union {
-            T v;
-            float4 q[sizeof(T) / 16];
-        } u;
-#pragma unroll
-        for (int i = 0; i < (int)(sizeof(T) / 16); i++) u.q[i] = __ldg(reinterpret_cast<const float4*>(p) + i);
-        return u.v;
-    } else if constexpr (sizeof(T) == 8) {
-        union {
-            T v;
-            int2 q;
-        } u;
-        u.q = __ldg(reinterpret_cast<const int2*>(p));
-        return u.v;
+        asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(sv.sbase + off));
     } else {
-        union {
-            T v;
-            uint32_t q[sizeof(T) / 4];
-        } u;
-#pragma unroll
-        for (int i = 0; i < (int)(sizeof(T) / 4); i++) u.q[i] = __ldg(reinterpret_cast<const uint32_t*>(p) + i);
-        return u.v;
+        v = __ldg(reinterpret_cast<const float4*>(sv.g + off));
     }
+    return v;
 }
-template <int SM, typename T>
-RTW_DEV T ld_hot(const T* p) { return ld_pod<(SM >= 1), T>(p); }
-template <int SM, typename T>
-RTW_DEV T ld_cold(const T* p) { return ld_pod<(SM >= 2), T>(p); }
+template <bool STAGED>
+RTW_DEV uint32_t ldb1(const SceneView& sv, uint32_t off) {
+    uint32_t v;
+    if constexpr (STAGED) {
+        asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(sv.sbase + off));
+    } else {
+        v = __ldg(reinterpret_cast<const uint32_t*>(sv.g + off));
+    }
+    return v;
+}
+template <bool STAGED>
+RTW_DEV uint2 ldb2(const SceneView& sv, uint32_t off) {
+    uint2 v;
+    if constexpr (STAGED) {
+        asm("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(sv.sbase + off));
+    } else {
+        v = __ldg(reinterpret_cast<const uint2*>(sv.g + off));
+    }
+    return v;
+}
+template <bool STAGED>
+RTW_DEV uint32_t ldb_u8(const SceneView& sv, uint32_t off) {
+    uint32_t v;
+    if constexpr (STAGED) {
+        asm("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(sv.sbase + off));
+    } else {
+        v = __ldg(sv.g + off);
+    }
+    return v;
+}
+template <bool STAGED>
+RTW_DEV double ldb_f64(const SceneView& sv, uint32_t off) {
+    uint2 v = ldb2<STAGED>(sv, off);
+    return __hiloint2double((int)v.y, (int)v.x);
+}
+template <int SM> RTW_DEV float4 hot4(const SceneView& sv, uint32_t off) { return ldb4<(SM >= 1)>(sv, off); }
+template <int SM> RTW_DEV uint32_t hot1(const SceneView& sv, uint32_t off) { return ldb1<(SM >= 1)>(sv, off); }
+template <int SM> RTW_DEV uint2 hot2(const SceneView& sv, uint32_t off) { return ldb2<(SM >= 1)>(sv, off); }
+template <int SM> RTW_DEV float4 cold4(const SceneView& sv, uint32_t off) { return ldb4<(SM >= 2)>(sv, off); }
+template <int SM> RTW_DEV uint32_t cold1(const SceneView& sv, uint32_t off) { return ldb1<(SM >= 2)>(sv, off); }
+template <int SM> RTW_DEV uint32_t cold_u8(const SceneView& sv, uint32_t off) { return ldb_u8<(SM >= 2)>(sv, off); }
+template <int SM> RTW_DEV double cold_f64(const SceneView& sv, uint32_t off) { return ldb_f64<(SM >= 2)>(sv, off); }
+RTW_DEV int fi(float f) { return __float_as_int(f); }
+
 template <int SM>
-RTW_DEV int ld_u8(const uint8_t* p) {  // cold section bytes (Perlin permutations)
-    if constexpr (SM >= 2) return *p;
-    else return __ldg(p);
+RTW_DEV DevXf ld_xf(const SceneView& sv, uint32_t off) {
+    float4 a = hot4<SM>(sv, off);
+    DevXf x;
+    x.c = a.x, x.s = a.y, x.tx = a.z, x.ty = a.w;
+    x.tz = __uint_as_float(hot1<SM>(sv, off + 16));
+    return x;
+}
+template <int SM>
+RTW_DEV DevItem ld_item(const SceneView& sv, uint32_t off) {
+    float4 a = hot4<SM>(sv, off), b = hot4<SM>(sv, off + 16);
+    DevItem it;
+    it.type = fi(a.x), it.xf = fi(a.y), it.first = fi(a.z), it.end = fi(a.w);
+    it.material = fi(b.x), it.flip = fi(b.y), it.density_eff = b.z, it.pad = 0.0f;
+    return it;
+}
+template <int SM>
+RTW_DEV DevLight ld_light(const SceneView& sv, uint32_t off) {
+    float4 a = hot4<SM>(sv, off), b = hot4<SM>(sv, off + 16);
+    DevLight l;
+    l.a0 = a.x, l.a1 = a.y, l.a2 = a.z, l.a3 = a.w;
+    l.k = b.x, l.area = b.y, l.type = fi(b.z), l.pad = 0;
+    return l;
+}
+template <int SM>
+RTW_DEV DevMat ld_mat(const SceneView& sv, uint32_t off) {
+    float4 a = cold4<SM>(sv, off), b = cold4<SM>(sv, off + 16);
+    DevMat m;
+    m.r = a.x, m.g = a.y, m.b = a.z, m.param = a.w;
+    m.type = fi(b.x), m.texture = fi(b.y), m.tex_is_constant = fi(b.z), m.pad = 0;
+    return m;
+}
+template <int SM>
+RTW_DEV DevTex ld_tex(const SceneView& sv, uint32_t off) {
+    float4 a = cold4<SM>(sv, off), b = cold4<SM>(sv, off + 16);
+    uint2 c = ldb2<(SM >= 2)>(sv, off + 32);
+    DevTex t;
+    t.r = a.x, t.g = a.y, t.b = a.z, t.scale = a.w;
+    t.type = fi(b.x), t.even = fi(b.y), t.odd = fi(b.z), t.image_offset = fi(b.w);
+    t.nx = (int)c.x, t.ny = (int)c.y, t.pad0 = t.pad1 = 0;
+    return t;
 }
 
 // ------------------------------------------------------------------------------------------------ transforms
@@ -139,23 +207,23 @@ RTW_DEV bool sphere_roots(V3 oc, V3 d, float a, float inv_a, float radius, float
     if (!(disc > 0.0f)) return false;
     float sq = sqrtf(disc);
     float c = dot(oc, oc) - r2;
-    if (b < 0.0f) {
-        float q = sq - b;
-        t1 = q * inv_a;
-        t0 = c / q;
-    } else {
-        float q = -b - sq;
-        t0 = q * inv_a;
-        t1 = c / q;
-    }
+    // q = -b - sign(b) sqrt(disc) never cancels; the roots are q/a and c/q
+    float q = -(b + copysignf(sq, b));
+    float ta = q * inv_a, tb = c * rcp_fast(q);
+    bool neg = b < 0.0f;  // q > 0: q/a is the far root
+    t0 = neg ? tb : ta;
+    t1 = neg ? ta : tb;
     return true;
 }
-RTW_DEV bool sphere_roots_f64(V3 o, V3 d, const double* pd, float& t0, float& t1) {
-    double ocx = (double)o.x - pd[0], ocy = (double)o.y - pd[1], ocz = (double)o.z - pd[2];
+template <int SM>
+RTW_DEV bool sphere_roots_f64(const SceneView& sv, uint32_t pd_off, V3 o, V3 d, float& t0, float& t1) {
+    double cx = cold_f64<SM>(sv, pd_off), cy = cold_f64<SM>(sv, pd_off + 8), cz = cold_f64<SM>(sv, pd_off + 16);
+    double rad = cold_f64<SM>(sv, pd_off + 24);
+    double ocx = (double)o.x - cx, ocy = (double)o.y - cy, ocz = (double)o.z - cz;
     double dx = d.x, dy = d.y, dz = d.z;
     double a = dx * dx + dy * dy + dz * dz;
     double b = ocx * dx + ocy * dy + ocz * dz;
-    double c = ocx * ocx + ocy * ocy + ocz * ocz - pd[3] * pd[3];
+    double c = ocx * ocx + ocy * ocy + ocz * ocz - rad * rad;
     double disc = b * b - a * c;
     if (!(disc > 0.0)) return false;
     double sq = sqrt(disc);
@@ -165,28 +233,33 @@ RTW_DEV bool sphere_roots_f64(V3 o, V3 d, const double* pd, float& t0, float& t1
 }
 // Pick the root the reference would return; false if neither lies in (tmin, tmax).
 RTW_DEV bool sphere_pick(float t0, float t1, float tmin, float tmax, float& t) {
-    if (t0 < tmax && t0 > tmin) {
-        t = t0;
-        return true;
-    }
-    if (t1 < tmax && t1 > tmin) {
-        t = t1;
-        return true;
-    }
-    return false;
+    bool ok0 = (t0 < tmax) & (t0 > tmin);
+    bool ok1 = (t1 < tmax) & (t1 > tmin);
+    t = ok0 ? t0 : t1;
+    return ok0 | ok1;
 }
 
 // x?_rect::hit (hittable.h:149-165, 184-200, 241-257): INCLUSIVE bounds; a NaN t passes like the reference (Q39).
 // (on, dn) are the ray's origin/direction along the plane normal, (oa, da), (ob, db) along the two in-plane axes;
 // inv_n = 1/dn is shared by every rect of that orientation in the group.  (k - on) * inv_n is exactly 0 for a ray
 // that starts on the plane and +-inf / NaN for dn == 0 exactly as the division is.
-RTW_DEV bool rect_test(float4 ra, float k, float on, float inv_n, float oa, float da, float ob, float db, float tmin,
-                       float tmax, float& t_out) {
+// The six ordered comparisons are chained into one predicate (FSETP with a predicate operand) and the running
+// closest hit is updated under it: 4 FP32 ops + 6 FSETP + 2 predicated moves per rect.
+RTW_DEV void rect_update(float4 ra, float k, int id, float on, float inv_n, float oa, float da, float ob, float db, float tmin,
+                         float& t_best, int& prim_best) {
     float t = (k - on) * inv_n;
     float a = fmaf(t, da, oa), b = fmaf(t, db, ob);
-    bool miss = (t < tmin) | (t > tmax) | (a < ra.x) | (a > ra.y) | (b < ra.z) | (b > ra.w);
-    t_out = t;
-    return !miss;
+    asm("{\n\t.reg .pred p;\n\t"
+        "setp.lt.ftz.f32 p, %2, %4;\n\t"
+        "setp.gt.or.ftz.f32 p, %2, %0, p;\n\t"
+        "setp.lt.or.ftz.f32 p, %5, %7, p;\n\t"
+        "setp.gt.or.ftz.f32 p, %5, %8, p;\n\t"
+        "setp.lt.or.ftz.f32 p, %6, %9, p;\n\t"
+        "setp.gt.or.ftz.f32 p, %6, %10, p;\n\t"
+        "@!p mov.f32 %0, %2;\n\t"
+        "@!p mov.b32 %1, %3;\n\t}"
+        : "+f"(t_best), "+r"(prim_best)
+        : "f"(t), "r"(id), "f"(tmin), "f"(a), "f"(b), "f"(ra.x), "f"(ra.y), "f"(ra.z), "f"(ra.w));
 }
 
 // aabb::hit (aabb.h:17-47) with std::max/std::min written out so NaN behaves as in the reference (Q32).
@@ -220,8 +293,8 @@ RTW_DEV bool aabb_hit(float4 lo, float4 hi, V3 o, V3 inv, float tmin, float tmax
 // from the id (complete_hit), so the search loop carries two registers.
 struct HitId {
     float t;
-    int prim;  // >= 0 primitive; -1 miss; <= -2: medium item ~prim
-    int item;  // item that owns the hit (its xf applies)
+    int prim;  // >= 0 primitive; -1 miss; <= -2: medium item -2 - prim
+    int item;  // index of the item that owns the hit (its xf applies)
 };
 
 // Per-ray constants of the primitive tests: reciprocal direction (rect planes, aabb slabs), a = d.d and 1/a (spheres).
@@ -232,40 +305,49 @@ struct RayK {
 RTW_DEV RayK make_rayk(V3 o, V3 d) {
     RayK k;
     k.o = o, k.d = d;
-    k.inv = mk(__frcp_rn(d.x), __frcp_rn(d.y), __frcp_rn(d.z));  // aabb.h:22 (1.0 / direction)
+    k.inv = mk(rcp_fast(d.x), rcp_fast(d.y), rcp_fast(d.z));  // aabb.h:22 (1.0 / direction)
     k.a = dot(d, d);
-    k.inv_a = __frcp_rn(k.a);
+    k.inv_a = rcp_fast(k.a);
+    return k;
+}
+// Ray constants in the object space of a translate/rotate_y chain: y is untouched by rotate_y, so 1/d.y carries over.
+RTW_DEV RayK xf_rayk(const DevXf& x, const RayK& w) {
+    RayK k;
+    xf_ray(x, w.o, w.d, k.o, k.d);
+    k.inv = mk(rcp_fast(k.d.x), w.inv.y, rcp_fast(k.d.z));
+    k.a = dot(k.d, k.d);
+    k.inv_a = rcp_fast(k.a);
     return k;
 }
 
-// hittable_list::hit (hittable_list.h:16-24) over groups [first, first+count): tmax shrinks to the running closest
-// hit — rects accept t == closest (a later object wins a tie), spheres need t < closest (Q38).  Inside a group the
-// records are ordered spheres, moving spheres, xy, xz, yz rects, each in list order, which evaluates the same
+// hittable_list::hit (hittable_list.h:16-24) over the groups at byte offsets [gfirst, gend): tmax shrinks to the running
+// closest hit — rects accept t == closest (a later object wins a tie), spheres need t < closest (Q38).  Inside a group
+// the records are ordered spheres, moving spheres, xy, xz, yz rects, each in list order, which evaluates the same
 // winner as the reference's interleaved order (see device_scene.hpp).  The second pass of hittable_list::hit
 // (:26-34) re-selects the same winner for deterministic children.
-// All loop bounds and record addresses are warp-uniform: one broadcast load per record.
+// All loop bounds and record addresses are warp-uniform: one broadcast load per 16 bytes.  Loops are kept rolled
+// (`unroll 1`): trip counts are tiny (Cornell: 1-3) and unrolled remainders cost more branches than they save.
 template <uint32_t F, int SM>
-RTW_DEV void test_groups(const SceneView& sv, int first, int count, const RayK& rk, float time, float tmin, float& t_best,
-                         int& prim_best) {
-    for (int gi = first; gi < first + count; gi++) {
-        DevGroup g = ld_hot<SM>(&sv.groups[gi]);
+RTW_DEV void test_groups(const SceneView& sv, uint32_t gfirst, uint32_t gend, const RayK& rk, float time, float tmin,
+                         float& t_best, int& prim_best) {
+#pragma unroll 1
+    for (uint32_t ga = gfirst; ga < gend; ga += 32) {
+        float4 g0 = hot4<SM>(sv, ga), g1 = hot4<SM>(sv, ga + 16);
         RayK k = rk;
-        if ((F & F_XF) && g.xf >= 0) {
-            DevXf x = ld_hot<SM>(&sv.xfs[g.xf]);
-            V3 ol, dl;
-            xf_ray(x, rk.o, rk.d, ol, dl);
-            k = make_rayk(ol, dl);
-        }
-        for (int r = g.sph0; r < g.sph1; r++) {
-            DevRec rec = ld_hot<SM>(&sv.recs[r]);
-            int id = __float_as_int(rec.b.w);
+        if ((F & F_XF) && fi(g0.x) >= 0) k = xf_rayk(ld_xf<SM>(sv, (uint32_t)fi(g0.x)), rk);
+        const uint32_t sph0 = (uint32_t)fi(g0.y), sph1 = (uint32_t)fi(g0.z), msph1 = (uint32_t)fi(g0.w);
+        const uint32_t xy1 = (uint32_t)fi(g1.x), xz1 = (uint32_t)fi(g1.y), yz1 = (uint32_t)fi(g1.z);
+#pragma unroll 1
+        for (uint32_t r = sph0; r < sph1; r += 32) {
+            float4 ra = hot4<SM>(sv, r), rb = hot4<SM>(sv, r + 16);
+            int id = fi(rb.w);
             float t0, t1, t;
             bool roots;
             if ((F & F_PRECISE) && (id & REC_PRECISE)) {
-                roots = sphere_roots_f64(k.o, k.d, sv.pd + 4 * __float_as_int(rec.b.x), t0, t1);
+                roots = sphere_roots_f64<SM>(sv, (uint32_t)fi(rb.x), k.o, k.d, t0, t1);
                 id &= ~REC_PRECISE;
             } else {
-                roots = sphere_roots(k.o - mk(rec.a.x, rec.a.y, rec.a.z), k.d, k.a, k.inv_a, rec.a.w, t0, t1);
+                roots = sphere_roots(k.o - mk(ra.x, ra.y, ra.z), k.d, k.a, k.inv_a, ra.w, t0, t1);
             }
             if (roots && sphere_pick(t0, t1, tmin, t_best, t)) {
                 t_best = t;
@@ -273,40 +355,32 @@ RTW_DEV void test_groups(const SceneView& sv, int first, int count, const RayK& 
             }
         }
         if (F & F_MOVING) {
-            for (int r = g.sph1; r < g.msph1; r++) {
-                DevRec rec = ld_hot<SM>(&sv.recs[r]);
+#pragma unroll 1
+            for (uint32_t r = sph1; r < msph1; r += 32) {
+                float4 ra = hot4<SM>(sv, r), rb = hot4<SM>(sv, r + 16);
                 // sphere.h:22-25 folded to c' + time*delta on the host
-                V3 c = madd(mk(rec.a.x, rec.a.y, rec.a.z), time, mk(rec.b.x, rec.b.y, rec.b.z));
+                V3 c = madd(mk(ra.x, ra.y, ra.z), time, mk(rb.x, rb.y, rb.z));
                 float t0, t1, t;
-                if (sphere_roots(k.o - c, k.d, k.a, k.inv_a, rec.a.w, t0, t1) && sphere_pick(t0, t1, tmin, t_best, t)) {
+                if (sphere_roots(k.o - c, k.d, k.a, k.inv_a, ra.w, t0, t1) && sphere_pick(t0, t1, tmin, t_best, t)) {
                     t_best = t;
-                    prim_best = __float_as_int(rec.b.w);
+                    prim_best = fi(rb.w);
                 }
             }
         }
-        for (int r = g.msph1; r < g.xy1; r++) {  // xy_rect: plane z = k
-            DevRec rec = ld_hot<SM>(&sv.recs[r]);
-            float t;
-            if (rect_test(rec.a, rec.b.x, k.o.z, k.inv.z, k.o.x, k.d.x, k.o.y, k.d.y, tmin, t_best, t)) {
-                t_best = t;
-                prim_best = __float_as_int(rec.b.w);
-            }
+#pragma unroll 1
+        for (uint32_t r = msph1; r < xy1; r += 32) {  // xy_rect: plane z = k
+            float4 ra = hot4<SM>(sv, r), rb = hot4<SM>(sv, r + 16);
+            rect_update(ra, rb.x, fi(rb.w), k.o.z, k.inv.z, k.o.x, k.d.x, k.o.y, k.d.y, tmin, t_best, prim_best);
         }
-        for (int r = g.xy1; r < g.xz1; r++) {  // xz_rect: plane y = k
-            DevRec rec = ld_hot<SM>(&sv.recs[r]);
-            float t;
-            if (rect_test(rec.a, rec.b.x, k.o.y, k.inv.y, k.o.x, k.d.x, k.o.z, k.d.z, tmin, t_best, t)) {
-                t_best = t;
-                prim_best = __float_as_int(rec.b.w);
-            }
+#pragma unroll 1
+        for (uint32_t r = xy1; r < xz1; r += 32) {  // xz_rect: plane y = k
+            float4 ra = hot4<SM>(sv, r), rb = hot4<SM>(sv, r + 16);
+            rect_update(ra, rb.x, fi(rb.w), k.o.y, k.inv.y, k.o.x, k.d.x, k.o.z, k.d.z, tmin, t_best, prim_best);
         }
-        for (int r = g.xz1; r < g.yz1; r++) {  // yz_rect: plane x = k
-            DevRec rec = ld_hot<SM>(&sv.recs[r]);
-            float t;
-            if (rect_test(rec.a, rec.b.x, k.o.x, k.inv.x, k.o.y, k.d.y, k.o.z, k.d.z, tmin, t_best, t)) {
-                t_best = t;
-                prim_best = __float_as_int(rec.b.w);
-            }
+#pragma unroll 1
+        for (uint32_t r = xz1; r < yz1; r += 32) {  // yz_rect: plane x = k
+            float4 ra = hot4<SM>(sv, r), rb = hot4<SM>(sv, r + 16);
+            rect_update(ra, rb.x, fi(rb.w), k.o.x, k.inv.x, k.o.y, k.d.y, k.o.z, k.d.z, tmin, t_best, prim_best);
         }
     }
 }

@@ -22,16 +22,13 @@ RTW_DEV bool path_step(const DevScene& sc, const SceneView& sv, const Rng& rng, 
         L = L + beta * background(sc, ray.d);
         return false;
     }
-    int mat_idx;
-    {
-        // material first: whether u,v are needed depends on its texture
-        if (h.prim < 0) mat_idx = ld_hot<SM>(&sv.items[-2 - h.prim].material);
-        else mat_idx = (int)(ld_cold<SM>(&sv.pm[h.prim]) >> PM_MAT_SHIFT);
-    }
-    DevMat m = ld_cold<SM>(&sv.mats[mat_idx]);
-    bool need_uv = (F & F_TEXTURES) && !m.tex_is_constant &&
-                   (m.type == RTW_MAT_LAMBERTIAN || m.type == RTW_MAT_DIFFUSE_LIGHT || m.type == RTW_MAT_ISOTROPIC);
-    HitRec rec = complete_hit<F, SM>(sv, h, ray.o, ray.d, ray.time, need_uv);
+    // material first: whether u,v are needed depends on its texture
+    uint32_t pm;
+    const int mat_idx = hit_material<SM>(sc, sv, h, pm);
+    const DevMat m = ld_mat<SM>(sv, sc.off[SEC_MATS] + (uint32_t)mat_idx * 32u);
+    const bool need_uv = (F & F_TEXTURES) && !m.tex_is_constant &&
+                         (m.type == RTW_MAT_LAMBERTIAN || m.type == RTW_MAT_DIFFUSE_LIGHT || m.type == RTW_MAT_ISOTROPIC);
+    const HitRec rec = complete_hit<F, SM>(sc, sv, h, pm, ray.o, ray.d, ray.time, need_uv);
 
     if (sc.render_type == RTW_RENDER_NORMAL) {  // :135-136
         L = L + beta * (0.5f * (rec.n + mk(1.0f, 1.0f, 1.0f)));
@@ -40,7 +37,7 @@ RTW_DEV bool path_step(const DevScene& sc, const SceneView& sv, const Rng& rng, 
 
     switch (m.type) {
         case RTW_MAT_DIFFUSE_LIGHT: {  // material.h:232-244: no scatter; one-sided emission (Q23)
-            if (dot(rec.n, ray.d) > 0.0f) L = L + beta * material_texture<SM>(sv, m, rec.u, rec.v, rec.p);
+            if (dot(rec.n, ray.d) > 0.0f) L = L + beta * material_texture<F, SM>(sc, sv, m, rec.u, rec.v, rec.p);
             return false;  // :62-63
         }
         case RTW_MAT_METAL: {  // material.h:128-136 -> specular branch :114-115
@@ -93,31 +90,23 @@ RTW_DEV bool path_step(const DevScene& sc, const SceneView& sv, const Rng& rng, 
         }
         case RTW_MAT_ISOTROPIC: {  // material.h:257-262
             U4 b = rng.draw(bounce, SITE_BALL);
-            beta = beta * material_texture<SM>(sv, m, rec.u, rec.v, rec.p);
+            beta = beta * material_texture<F, SM>(sc, sv, m, rec.u, rec.v, rec.p);
             ray.o = rec.p;
             ray.d = random_in_unit_ball(b.x, b.y, b.z);
             return true;
         }
         default: {  // lambertian: material.h:81-119 + mixture importance sampling :117-132
-            V3 att = material_texture<SM>(sv, m, rec.u, rec.v, rec.p);
-            U4 r = rmain;
-            Onb uvw = onb_from_w(rec.n);  // cosine_pdf ctor (pdf.h:18)
-            bool have_lights = sc.n_lights > 0;  // :118
-            V3 dir;
-            if (!have_lights || r.x < 0.5f) {  // mixture_pdf::generate (pdf.h:69-75): p[0] = cosine
-                dir = onb_local(uvw, random_cosine_direction(r.z, r.w));
-            } else {
-                dir = lights_random<SM>(sc, sv, rec.p, r.y, r.z, r.w);
-            }
-            V3 nd = normalize(dir);
-            float cos_w = dot(nd, uvw.w);
-            float pdf_cos = (cos_w <= 0.0f) ? 0.0f : cos_w / kPi;  // cosine_pdf::value (pdf.h:20-24)
+            const V3 att = material_texture<F, SM>(sc, sv, m, rec.u, rec.v, rec.p);
+            const V3 dir = mixture_generate<SM>(sc, sv, rec.p, rec.n, rmain);  // :120-122
+            const V3 nd = normalize(dir);
+            const float cos_w = dot(nd, normalize(rec.n));                // cosine_pdf: uvw.w = normalize(n) (pdf.h:18)
+            const float pdf_cos = (cos_w <= 0.0f) ? 0.0f : cos_w / kPi;    // cosine_pdf::value (pdf.h:20-24)
             float pdf_val = pdf_cos;
-            if (have_lights) pdf_val = 0.5f * pdf_cos + 0.5f * lights_pdf<SM>(sc, sv, rec.p, dir);  // pdf.h:64-67
+            if (sc.n_lights > 0) pdf_val = 0.5f * pdf_cos + 0.5f * lights_pdf<SM>(sc, sv, rec.p, dir);  // pdf.h:64-67
             if (pdf_val <= 0.0f) return false;  // :126-127 (emitted is zero for a lambertian)
-            float cos_n = dot(rec.n, nd);
-            float spdf = (cos_n < 0.0f) ? 0.0f : cos_n / kPi;  // lambertian::scattering_pdf (material.h:115-119)
-            beta = beta * att * (spdf / pdf_val);  // :129-132
+            const float cos_n = dot(rec.n, nd);
+            const float spdf = (cos_n < 0.0f) ? 0.0f : cos_n / kPi;  // lambertian::scattering_pdf (material.h:115-119)
+            beta = beta * att * (spdf * rcp_fast(pdf_val));      // :129-132
             ray.o = rec.p;
             ray.d = dir;  // NOT normalised (:123)
             return true;

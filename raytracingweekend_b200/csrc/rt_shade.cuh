@@ -10,28 +10,26 @@ constexpr float kPi = 3.14159265358979323846f;
 // perlin::noise (noise.h:89-151, InterpolationType::PERLIN) + perlin_interp (noise.h:40-60) with the Hermite
 // cubic `smooth` (noise.h:9-12, :19).
 template <int SM>
-RTW_DEV float perlin_noise(const SceneView& sv, V3 p) {
+RTW_DEV float perlin_noise(const DevScene& sc, const SceneView& sv, V3 p) {
     float fx = floorf(p.x), fy = floorf(p.y), fz = floorf(p.z);
     float u = p.x - fx, v = p.y - fy, w = p.z - fz;
     int i = (int)fx, j = (int)fy, k = (int)fz;
     float uu = u * u * (3.0f - 2.0f * u), vv = v * v * (3.0f - 2.0f * v), ww = w * w * (3.0f - 2.0f * w);
-    const uint8_t* px = sv.perlin_perm;
-    const uint8_t* py = sv.perlin_perm + 256;
-    const uint8_t* pz = sv.perlin_perm + 512;
+    const uint32_t px = sc.off[SEC_PERM], py = px + 256, pz = px + 512, rv = sc.off[SEC_RANVEC];
     float accum = 0.0f;
 #pragma unroll
     for (int di = 0; di < 2; di++) {
-        int hx = ld_u8<SM>(&px[(i + di) & 255]);
+        int hx = (int)cold_u8<SM>(sv, px + (uint32_t)((i + di) & 255));
         float wi = di ? uu : 1.0f - uu;
 #pragma unroll
         for (int dj = 0; dj < 2; dj++) {
-            int hy = ld_u8<SM>(&py[(j + dj) & 255]);
+            int hy = (int)cold_u8<SM>(sv, py + (uint32_t)((j + dj) & 255));
             float wj = dj ? vv : 1.0f - vv;
 #pragma unroll
             for (int dk = 0; dk < 2; dk++) {
-                int hz = ld_u8<SM>(&pz[(k + dk) & 255]);
+                int hz = (int)cold_u8<SM>(sv, pz + (uint32_t)((k + dk) & 255));
                 float wk = dk ? ww : 1.0f - ww;
-                float4 c = ld_cold<SM>(&sv.perlin_ranvec[hx ^ hy ^ hz]);
+                float4 c = cold4<SM>(sv, rv + (uint32_t)(hx ^ hy ^ hz) * 16u);
                 float dp = fmaf(c.x, u - di, fmaf(c.y, v - dj, c.z * (w - dk)));
                 accum = fmaf(wi * wj * wk, dp, accum);
             }
@@ -40,10 +38,10 @@ RTW_DEV float perlin_noise(const SceneView& sv, V3 p) {
     return accum;
 }
 template <int SM>
-RTW_DEV float perlin_turb(const SceneView& sv, V3 p) {  // noise.h:74-86, depth 7
+RTW_DEV float perlin_turb(const DevScene& sc, const SceneView& sv, V3 p) {  // noise.h:74-86, depth 7
     float accum = 0.0f, weight = 1.0f;
     for (int i = 0; i < 7; i++) {
-        accum = fmaf(weight, perlin_noise<SM>(sv, p), accum);
+        accum = fmaf(weight, perlin_noise<SM>(sc, sv, p), accum);
         weight *= 0.5f;
         p = p * 2.0f;
     }
@@ -52,9 +50,9 @@ RTW_DEV float perlin_turb(const SceneView& sv, V3 p) {  // noise.h:74-86, depth 
 
 // texture::value(u, v, p) (texture.h:21-24, 35-46, 57-68, 81-94)
 template <int SM>
-RTW_DEV V3 texture_value(const SceneView& sv, int tex, float u, float v, V3 p) {
+RTW_DEV V3 texture_value(const DevScene& sc, const SceneView& sv, int tex, float u, float v, V3 p) {
     for (int guard = 0; guard < 16; guard++) {
-        DevTex t = ld_cold<SM>(&sv.texs[tex]);
+        DevTex t = ld_tex<SM>(sv, sc.off[SEC_TEXS] + (uint32_t)tex * 48u);
         if (t.type == RTW_TEX_CONSTANT) return mk(t.r, t.g, t.b);
         if (t.type == RTW_TEX_CHECKER) {
             float sines = sinf(10.0f * p.x) * sinf(10.0f * p.y) * sinf(10.0f * p.z);
@@ -62,7 +60,7 @@ RTW_DEV V3 texture_value(const SceneView& sv, int tex, float u, float v, V3 p) {
             continue;
         }
         if (t.type == RTW_TEX_NOISE) {
-            float g = 0.5f * (1.0f + sinf(fmaf(t.scale, p.z, 10.0f * perlin_turb<SM>(sv, p))));
+            float g = 0.5f * (1.0f + sinf(fmaf(t.scale, p.z, 10.0f * perlin_turb<SM>(sc, sv, p))));
             return mk(g, g, g);
         }
         // image_texture (texture.h:81-94): nearest texel, v flipped
@@ -76,44 +74,28 @@ RTW_DEV V3 texture_value(const SceneView& sv, int tex, float u, float v, V3 p) {
     return mk(0.0f, 0.0f, 0.0f);
 }
 
-template <int SM>
-RTW_DEV V3 material_texture(const SceneView& sv, const DevMat& m, float u, float v, V3 p) {
-    if (m.tex_is_constant) return mk(m.r, m.g, m.b);
-    return texture_value<SM>(sv, m.texture, u, v, p);
+template <uint32_t F, int SM>
+RTW_DEV V3 material_texture(const DevScene& sc, const SceneView& sv, const DevMat& m, float u, float v, V3 p) {
+    if (!(F & F_TEXTURES) || m.tex_is_constant) return mk(m.r, m.g, m.b);
+    return texture_value<SM>(sc, sv, m.texture, u, v, p);
 }
 
 // ------------------------------------------------------------------------------------------------ sampling
 struct Onb {  // onb.h:32-38
     V3 u, v, w;
 };
+// onb::build_from_w with the two possible helper axes folded in: cross(w, x^) = (0, w.z, -w.y), cross(w, y^) = (-w.z, 0, w.x).
 RTW_DEV Onb onb_from_w(V3 n) {
     Onb b;
     b.w = normalize(n);
-    V3 a = (fabsf(b.w.x) > 0.9f) ? mk(0.0f, 1.0f, 0.0f) : mk(1.0f, 0.0f, 0.0f);
-    b.v = normalize(cross(b.w, a));
+    const bool big = fabsf(b.w.x) > 0.9f;
+    V3 c = big ? mk(-b.w.z, 0.0f, b.w.x) : mk(0.0f, b.w.z, -b.w.y);
+    b.v = normalize(c);
     b.u = cross(b.w, b.v);
     return b;
 }
 RTW_DEV V3 onb_local(const Onb& b, V3 a) { return a.x * b.u + a.y * b.v + a.z * b.w; }  // onb.h:21-24
 
-RTW_DEV V3 random_cosine_direction(float r1, float r2) {  // utility.h:54-67
-    float z = sqrtf(1.0f - r2);
-    float s, c;
-    sincospif(2.0f * r1, &s, &c);
-    float sr = sqrtf(r2);
-    return mk(c * sr, s * sr, z);
-}
-// utility.h:69-82. 1 - cos_theta_max is formed as q/(1+sqrt(1-q)) (no cancellation for far spheres).
-RTW_DEV V3 random_to_sphere(float radius, float distance_squared, float r1, float r2) {
-    float q = radius * radius / distance_squared;
-    float one_minus_cmax = q / (1.0f + sqrtf(1.0f - q));
-    float omz = r2 * one_minus_cmax;
-    float z = 1.0f - omz;
-    float st = sqrtf(omz * (1.0f + z));  // sqrt(1 - z*z)
-    float s, c;
-    sincospif(2.0f * r1, &s, &c);
-    return mk(c * st, s * st, z);
-}
 // random_in_unit_sphere (utility.h:27-35) without the rejection loop: uniform direction * cbrt(U) is the same
 // distribution (uniform in the unit ball).
 RTW_DEV V3 random_in_unit_ball(float u0, float u1, float u2) {
@@ -127,58 +109,76 @@ RTW_DEV V3 random_in_unit_ball(float u0, float u1, float u2) {
 
 // ------------------------------------------------------------------------------------------------ light pdfs
 // xz_rect::pdf_value (hittable.h:208-222): self-hit test with t in [0.001, +inf], no occlusion.
-RTW_DEV float light_rect_pdf(const DevLight& l, V3 o, V3 v) {
-    float t = __fdiv_rn(l.k - o.y, v.y);
-    if (t < 0.001f || t > INFINITY) return 0.0f;
+// `len2` = dot(v, v), `len` = sqrt(len2): distance^2 / (cosine * area) = t^2 len2 len / (|v.y| area).
+RTW_DEV float light_rect_pdf(const DevLight& l, V3 o, V3 v, float len2, float len) {
+    float t = (l.k - o.y) * rcp_fast(v.y);
     float x = fmaf(t, v.x, o.x), z = fmaf(t, v.z, o.z);
-    if (x < l.a0 || x > l.a1 || z < l.a2 || z > l.a3) return 0.0f;
-    float len2 = dot(v, v);
-    float distance_squared = t * t * len2;
-    float cosine = fabsf(v.y * rsqrtf(len2));
-    return distance_squared / (cosine * l.area);
+    bool miss = (t < 0.001f) | (t > INFINITY) | (x < l.a0) | (x > l.a1) | (z < l.a2) | (z > l.a3);
+    float pdf = (t * t) * (len2 * len) * rcp_fast(fabsf(v.y) * l.area);
+    return miss ? 0.0f : pdf;
 }
 // sphere_base::pdf_value (sphere.h:88-99)
-RTW_DEV float light_sphere_pdf(const DevLight& l, V3 o, V3 v) {
-    V3 c = mk(l.a0, l.a1, l.a2);
+RTW_DEV float light_sphere_pdf(const DevLight& l, V3 o, V3 v, float len2, float inv_len2) {
+    V3 co = mk(l.a0 - o.x, l.a1 - o.y, l.a2 - o.z);
     float t0, t1, t;
-    float a = dot(v, v);
-    if (!sphere_roots(o - c, v, a, __frcp_rn(a), l.a3, t0, t1) || !sphere_pick(t0, t1, 0.001f, INFINITY, t)) return 0.0f;
-    V3 co = c - o;
-    float q = l.a3 * l.a3 / dot(co, co);
-    float one_minus_cmax = q / (1.0f + sqrtf(1.0f - q));  // NaN when the origin is inside, like the reference (Q17)
-    return 1.0f / (2.0f * kPi * one_minus_cmax);
+    bool hit = sphere_roots(-co, v, len2, inv_len2, l.a3, t0, t1) && sphere_pick(t0, t1, 0.001f, INFINITY, t);
+    float q = l.a3 * l.a3 * rcp_fast(dot(co, co));
+    float one_minus_cmax = q * rcp_fast(1.0f + sqrtf(1.0f - q));  // NaN when the origin is inside, like the reference (Q17)
+    float pdf = rcp_fast(2.0f * kPi * one_minus_cmax);
+    return hit ? pdf : 0.0f;
 }
 // hittable_list::pdf_value (hittable_list.h:44-53)
 template <int SM>
 RTW_DEV float lights_pdf(const DevScene& sc, const SceneView& sv, V3 o, V3 v) {
-    float weight = 1.0f / (float)sc.n_lights;
+    const float weight = 1.0f / (float)sc.n_lights;
+    const float len2 = dot(v, v);
+    const float inv_len2 = rcp_fast(len2), len = sqrtf(len2);
     float sum = 0.0f;
+    const uint32_t l0 = sc.off[SEC_LIGHTS];
+#pragma unroll 1
     for (int i = 0; i < sc.n_lights; i++) {
-        DevLight l = ld_hot<SM>(&sv.lights[i]);
+        DevLight l = ld_light<SM>(sv, l0 + (uint32_t)i * 32u);
         float pv = 0.0f;  // hittable.h:36 default
-        if (l.type == RTW_LIGHT_XZ_RECT) pv = light_rect_pdf(l, o, v);
-        else if (l.type == RTW_LIGHT_SPHERE) pv = light_sphere_pdf(l, o, v);
+        if (l.type == RTW_LIGHT_XZ_RECT) pv = light_rect_pdf(l, o, v, len2, len);
+        else if (l.type == RTW_LIGHT_SPHERE) pv = light_sphere_pdf(l, o, v, len2, inv_len2);
         sum = fmaf(weight, pv, sum);
     }
     return sum;
 }
-// hittable_list::random (hittable_list.h:55-59) -> xz_rect::random (hittable.h:224-228) |
-// sphere_base::random (sphere.h:101-108) | hittable::random default (hittable.h:37)
+
+// mixture_pdf::generate (pdf.h:69-75) over cosine_pdf (pdf.h:26-29 -> utility.h:54-67) and hittable_pdf on the lights
+// list (hittable_list.h:55-59 -> xz_rect::random hittable.h:224-228 | sphere_base::random sphere.h:101-108 ->
+// utility.h:69-82 | hittable::random default hittable.h:37).
+// The cosine lobe and the cone towards a sphere light are the same computation — a polar direction (z, sqrt(1-z^2))
+// with azimuth 2*pi*r1 in an orthonormal frame about an axis — with different axis and z, so they run as ONE
+// instruction stream with selected operands (one frame, one sincospi) instead of two divergent branches:
+//   cosine:  axis = n,            z = sqrt(1 - r2),                  sin^2 = r2
+//   sphere:  axis = centre - o,   z = 1 - r2 (1 - cos_max),          sin^2 = (1 - z)(1 + z)
+// with 1 - cos_max = q / (1 + sqrt(1 - q)), q = radius^2 / |centre - o|^2 (no cancellation for far spheres).
+// u: .x mixture choice, .y light pick (utility.h:22-25 with a = 0, b = n-1), .z = r1, .w = r2.
 template <int SM>
-RTW_DEV V3 lights_random(const DevScene& sc, const SceneView& sv, V3 o, float upick, float r1, float r2) {
-    int n = sc.n_lights;
-    int idx = min(n - 1, (int)((float)n * upick));  // utility.h:22-25 with a = 0, b = n-1
-    DevLight l = ld_hot<SM>(&sv.lights[idx]);
-    if (l.type == RTW_LIGHT_XZ_RECT) {
-        V3 pt = mk(fmaf(l.a1 - l.a0, r1, l.a0), l.k, fmaf(l.a3 - l.a2, r2, l.a2));
-        return pt - o;
+RTW_DEV V3 mixture_generate(const DevScene& sc, const SceneView& sv, V3 o, V3 n, U4 u) {
+    int ltype = -1;  // -1: cosine lobe
+    DevLight l;
+    l.a0 = l.a1 = l.a2 = l.a3 = l.k = 0.0f;
+    if (sc.n_lights > 0 && !(u.x < 0.5f)) {
+        int idx = min(sc.n_lights - 1, (int)((float)sc.n_lights * u.y));
+        l = ld_light<SM>(sv, sc.off[SEC_LIGHTS] + (uint32_t)idx * 32u);
+        ltype = l.type;
     }
-    if (l.type == RTW_LIGHT_SPHERE) {
-        V3 dir = mk(l.a0, l.a1, l.a2) - o;
-        Onb uvw = onb_from_w(dir);
-        return onb_local(uvw, random_to_sphere(l.a3, dot(dir, dir), r1, r2));
-    }
-    return mk(1.0f, 0.0f, 0.0f);
+    if (ltype == RTW_LIGHT_XZ_RECT) return mk(fmaf(l.a1 - l.a0, u.z, l.a0) - o.x, l.k - o.y, fmaf(l.a3 - l.a2, u.w, l.a2) - o.z);
+    if (ltype == RTW_LIGHT_DEFAULT) return mk(1.0f, 0.0f, 0.0f);
+    const bool sph = ltype == RTW_LIGHT_SPHERE;
+    V3 axis = sph ? mk(l.a0 - o.x, l.a1 - o.y, l.a2 - o.z) : n;
+    float q = sph ? l.a3 * l.a3 * rcp_fast(dot(axis, axis)) : u.w;
+    float s1 = sqrtf(1.0f - q);
+    float omz = u.w * q * rcp_fast(1.0f + s1);
+    float z = sph ? 1.0f - omz : s1;
+    float st = sqrtf(sph ? omz * (1.0f + z) : u.w);
+    float sn, cs;
+    sincospif(2.0f * u.z, &sn, &cs);
+    Onb uvw = onb_from_w(axis);
+    return onb_local(uvw, mk(cs * st, sn * st, z));
 }
 
 // ------------------------------------------------------------------------------------------------ camera

@@ -13,6 +13,7 @@ constexpr int kStackDepth = 32;  // shared-memory traversal stack entries per th
 // by a relative margin that covers the 1/d-multiply vs divide rounding gap, so no candidate with
 // t <= best is ever culled and the winner is the reference's.
 // Stack: shared memory, one column per thread (`stack[level * stride]`), depth-first, left first.
+// References are byte offsets (DevNode): >= 0 node, < 0 ~leaf.
 template <uint32_t F, int SM, bool SHRINK>
 RTW_DEV void bvh_hit(const SceneView& sv, int root, const RayK& rk, float time, float tmin, float tmax, int* stack,
                      int stride, float& t_out, int& prim_out) {
@@ -23,10 +24,10 @@ RTW_DEV void bvh_hit(const SceneView& sv, int root, const RayK& rk, float time, 
     int ref = root;
     for (;;) {
         if (ref >= 0) {
-            float4 lo = ld_hot<SM>(&sv.node_lo[ref]), hi = ld_hot<SM>(&sv.node_hi[ref]);
+            float4 lo = hot4<SM>(sv, (uint32_t)ref), hi = hot4<SM>(sv, (uint32_t)ref + 16);
             float cull = (SHRINK && best_prim >= 0) ? fmaf(best, 4e-6f, best) : tmax;
             if (aabb_hit(lo, hi, o, inv, tmin, cull)) {
-                int l = __float_as_int(lo.w), r = __float_as_int(hi.w);
+                int l = fi(lo.w), r = fi(hi.w);
                 if (r != l) {  // n == 1 node has left == right (hittable.h:68-72): one visit is enough
                     stack[sp * stride] = r;
                     sp++;
@@ -35,7 +36,7 @@ RTW_DEV void bvh_hit(const SceneView& sv, int root, const RayK& rk, float time, 
                 continue;
             }
         } else {
-            int2 lf = ld_hot<SM>(&sv.leaves[~ref]);
+            uint2 lf = hot2<SM>(sv, (uint32_t)~ref);
             float t_leaf = tmax;
             int p_leaf = -1;
             test_groups<F, SM>(sv, lf.x, lf.y, rk, time, tmin, t_leaf, p_leaf);
@@ -69,44 +70,41 @@ RTW_DEV HitId closest_hit(const DevScene& sc, const SceneView& sv, V3 o, V3 d, f
     h.item = -1;
     int medium_idx = 0;
     const RayK rk = make_rayk(o, d);
+    const uint32_t items0 = sc.off[SEC_ITEMS];
+    constexpr bool kOnlyLists = (F & (F_BVH | F_MEDIA)) == 0;
+#pragma unroll 1
     for (int it = 0; it < sc.n_world_items; it++) {
-        DevItem item = ld_hot<SM>(&sv.items[it]);
-        if (item.type == RTW_ITEM_PRIMS) {
+        const uint32_t ia = items0 + (uint32_t)it * 32u;
+        float4 i0 = hot4<SM>(sv, ia);
+        const int type = fi(i0.x), ixf = fi(i0.y), first = fi(i0.z), end = fi(i0.w);
+        if (kOnlyLists || type == RTW_ITEM_PRIMS) {
             int before = h.prim;
-            test_groups<F, SM>(sv, item.first, item.count, rk, time, tmin, h.t, h.prim);
+            test_groups<F, SM>(sv, (uint32_t)first, (uint32_t)end, rk, time, tmin, h.t, h.prim);
             if (h.prim != before) h.item = it;
-        } else if ((F & F_BVH) && item.type == RTW_ITEM_BVH) {
+        } else if ((F & F_BVH) && type == RTW_ITEM_BVH) {
             RayK lk = rk;
-            if (item.xf >= 0) {
-                V3 ol, dl;
-                xf_ray(ld_hot<SM>(&sv.xfs[item.xf]), o, d, ol, dl);
-                lk = make_rayk(ol, dl);
-            }
+            if (ixf >= 0) lk = xf_rayk(ld_xf<SM>(sv, (uint32_t)ixf), rk);
             int p = -1;
             float t = h.t;
-            bvh_hit<F, SM, true>(sv, item.first, lk, time, tmin, h.t, stack, stride, t, p);
+            bvh_hit<F, SM, true>(sv, first, lk, time, tmin, h.t, stack, stride, t, p);
             if (p >= 0) {
                 h.t = t;
                 h.prim = p;
                 h.item = it;
             }
-        } else if ((F & F_MEDIA) && item.type == RTW_ITEM_MEDIUM) {
+        } else if ((F & F_MEDIA) && type == RTW_ITEM_MEDIUM) {
             // constant_medium::hit (hittable.h:430-479)
             int mi = medium_idx++;
             if (!rng) continue;
             RayK lk = rk;
-            if (item.xf >= 0) {
-                V3 ol, dl;
-                xf_ray(ld_hot<SM>(&sv.xfs[item.xf]), o, d, ol, dl);
-                lk = make_rayk(ol, dl);
-            }
+            if (ixf >= 0) lk = xf_rayk(ld_xf<SM>(sv, (uint32_t)ixf), rk);
             float t1 = FLT_MAX, t2 = FLT_MAX;
             int p1 = -1, p2 = -1;
-            test_groups<F, SM>(sv, item.first, item.count, lk, time, -FLT_MAX, t1, p1);  // :438-442
+            test_groups<F, SM>(sv, (uint32_t)first, (uint32_t)end, lk, time, -FLT_MAX, t1, p1);  // :438-442
             if (p1 < 0) continue;
             // :447 `rec1.t + 0.0001f`; in FP32 the step can vanish for |t| > ~800, so advance at least one ulp
             float step = fmaxf(t1 + 0.0001f, nextafterf(t1, FLT_MAX));
-            test_groups<F, SM>(sv, item.first, item.count, lk, time, step, t2, p2);  // :445-449
+            test_groups<F, SM>(sv, (uint32_t)first, (uint32_t)end, lk, time, step, t2, p2);  // :445-449
             if (p2 < 0) continue;
             if (t1 < tmin) t1 = tmin;  // :452-457
             if (t2 > h.t) t2 = h.t;
@@ -115,7 +113,8 @@ RTW_DEV HitId closest_hit(const DevScene& sc, const SceneView& sv, V3 o, V3 d, f
             float len = sqrtf(lk.a);
             float inside = (t2 - t1) * len;  // :463-464
             float u = rng->draw(bounce, SITE_MEDIUM0 + (uint32_t)mi).x;
-            float hit_distance = -(1.0f / item.density_eff) * logf(u);  // :465 with density*multiplicity (Q5)
+            float density_eff = __uint_as_float(hot1<SM>(sv, ia + 24));
+            float hit_distance = -(1.0f / density_eff) * logf(u);  // :465 with density*multiplicity (Q5)
             if (hit_distance < inside) {
                 h.t = t1 + hit_distance / len;  // :469
                 h.prim = -2 - it;
@@ -124,22 +123,20 @@ RTW_DEV HitId closest_hit(const DevScene& sc, const SceneView& sv, V3 o, V3 d, f
         }
     }
     if (EXACT_TIES && (F & F_BVH) && h.prim >= 0) {
+#pragma unroll 1
         for (int it = 0; it < sc.n_world_items; it++) {
-            DevItem item = ld_hot<SM>(&sv.items[it]);
-            if (item.type == RTW_ITEM_PRIMS) {
+            float4 i0 = hot4<SM>(sv, items0 + (uint32_t)it * 32u);
+            const int type = fi(i0.x), ixf = fi(i0.y), first = fi(i0.z), end = fi(i0.w);
+            if (type == RTW_ITEM_PRIMS) {
                 int before = h.prim;
-                test_groups<F, SM>(sv, item.first, item.count, rk, time, tmin, h.t, h.prim);
+                test_groups<F, SM>(sv, (uint32_t)first, (uint32_t)end, rk, time, tmin, h.t, h.prim);
                 if (h.prim != before) h.item = it;
-            } else if (item.type == RTW_ITEM_BVH) {
+            } else if (type == RTW_ITEM_BVH) {
                 RayK lk = rk;
-                if (item.xf >= 0) {
-                    V3 ol, dl;
-                    xf_ray(ld_hot<SM>(&sv.xfs[item.xf]), o, d, ol, dl);
-                    lk = make_rayk(ol, dl);
-                }
+                if (ixf >= 0) lk = xf_rayk(ld_xf<SM>(sv, (uint32_t)ixf), rk);
                 int p = -1;
                 float t = h.t;
-                bvh_hit<F, SM, false>(sv, item.first, lk, time, tmin, h.t, stack, stride, t, p);
+                bvh_hit<F, SM, false>(sv, first, lk, time, tmin, h.t, stack, stride, t, p);
                 if (p >= 0) {
                     h.t = t;
                     h.prim = p;
@@ -166,65 +163,86 @@ RTW_DEV void sphere_uv(V3 n, float& u, float& v) {  // sphere.h:115-122 / utilit
     v = (theta + PI / 2.0f) / PI;
 }
 
+// Material index of the hit (needed before complete_hit: whether u,v are wanted depends on the material's texture).
+template <int SM>
+RTW_DEV int hit_material(const DevScene& sc, const SceneView& sv, const HitId& h, uint32_t& pm_out) {
+    if (h.prim < 0) {
+        pm_out = 0;
+        return (int)hot1<SM>(sv, sc.off[SEC_ITEMS] + (uint32_t)(-2 - h.prim) * 32u + 16u);
+    }
+    pm_out = cold1<SM>(sv, sc.off[SEC_PM] + (uint32_t)h.prim * 4u);
+    return (int)(pm_out >> PM_MAT_SHIFT);
+}
+
 template <uint32_t F, int SM>
-RTW_DEV HitRec complete_hit(const SceneView& sv, const HitId& h, V3 o, V3 d, float time, bool need_uv) {
+RTW_DEV HitRec complete_hit(const DevScene& sc, const SceneView& sv, const HitId& h, uint32_t m, V3 o, V3 d, float time,
+                            bool need_uv) {
     HitRec r;
     r.u = r.v = 0.0f;
-    if (h.prim < 0) {  // constant_medium (hittable.h:469-472): arbitrary normal, u/v never written (Q13)
-        DevItem item = ld_hot<SM>(&sv.items[-2 - h.prim]);
+    if ((F & F_MEDIA) && h.prim < 0) {  // constant_medium (hittable.h:469-472): arbitrary normal, u/v never written (Q13)
+        const uint32_t ia = sc.off[SEC_ITEMS] + (uint32_t)(-2 - h.prim) * 32u;
+        uint2 mf = hot2<SM>(sv, ia + 16);
         r.p = madd(o, h.t, d);
-        r.n = mk(item.flip ? -1.0f : 1.0f, 0.0f, 0.0f);
-        r.mat = item.material;
+        r.n = mk(mf.y ? -1.0f : 1.0f, 0.0f, 0.0f);
+        r.mat = (int)mf.x;
         return r;
     }
-    uint32_t m = ld_cold<SM>(&sv.pm[h.prim]);
-    int type = m & PM_TYPE_MASK;
+    const int type = m & PM_TYPE_MASK;
     r.mat = (int)(m >> PM_MAT_SHIFT);
     // object-space ray: item transform, then the primitive's own chain
     V3 ol = o, dl = d;
     int ixf = -1, pxf = 0;
+    DevXf xi, xp;
     if (F & F_XF) {
-        ixf = ld_hot<SM>(&sv.items[h.item].xf);
-        if (ixf >= 0) xf_ray(ld_hot<SM>(&sv.xfs[ixf]), o, d, ol, dl);
+        if (F & (F_BVH | F_MEDIA)) {  // only BVH / medium items carry an item-level transform
+            ixf = (int)hot1<SM>(sv, sc.off[SEC_ITEMS] + (uint32_t)h.item * 32u + 4u);
+            if (ixf >= 0) {
+                xi = ld_xf<SM>(sv, (uint32_t)ixf);
+                xf_ray(xi, o, d, ol, dl);
+            }
+        }
         pxf = (m >> PM_XF_SHIFT) & PM_XF_MASK;
         if (pxf) {
+            xp = ld_xf<SM>(sv, sc.off[SEC_XFS] + (uint32_t)(pxf - 1) * 32u);
             V3 o2, d2;
-            xf_ray(ld_hot<SM>(&sv.xfs[pxf - 1]), ol, dl, o2, d2);
+            xf_ray(xp, ol, dl, o2, d2);
             ol = o2, dl = d2;
         }
     }
-    float4 pa = ld_cold<SM>(&sv.pa[h.prim]);
+    float4 pa = cold4<SM>(sv, sc.off[SEC_PA] + (uint32_t)h.prim * 16u);
     V3 pl = madd(ol, h.t, dl);  // point_at_parameter in object space
     V3 nl;
     if (type <= RTW_PRIM_MOVING_SPHERE) {
         V3 c = mk(pa.x, pa.y, pa.z);
         float radius = pa.w;
         if ((F & F_MOVING) && type == RTW_PRIM_MOVING_SPHERE) {
-            float4 pb = ld_cold<SM>(&sv.pb[h.prim]);
+            float4 pb = cold4<SM>(sv, sc.off[SEC_PB] + (uint32_t)h.prim * 16u);
             c = madd(c, time, mk(pb.x, pb.y, pb.z));
         }
-        float inv_r = 1.0f / radius;
+        float inv_r = rcp_fast(radius);
         if ((F & F_PRECISE) && (m & PM_PRECISE)) {
-            float4 pb = ld_cold<SM>(&sv.pb[h.prim]);
-            const double* pd = sv.pd + 4 * __float_as_int(pb.w);
+            float4 pb = cold4<SM>(sv, sc.off[SEC_PB] + (uint32_t)h.prim * 16u);
+            const uint32_t pd = (uint32_t)fi(pb.w);
+            double cx = cold_f64<SM>(sv, pd), cy = cold_f64<SM>(sv, pd + 8), cz = cold_f64<SM>(sv, pd + 16);
+            double rad = cold_f64<SM>(sv, pd + 24);
             // p - centre in FP64: at r = 1000 the FP32 difference would quantise the normal to ~1e-4
             double t = h.t;
-            nl = mk((float)(((double)ol.x + t * dl.x - pd[0]) / pd[3]), (float)(((double)ol.y + t * dl.y - pd[1]) / pd[3]),
-                    (float)(((double)ol.z + t * dl.z - pd[2]) / pd[3]));
+            nl = mk((float)(((double)ol.x + t * dl.x - cx) / rad), (float)(((double)ol.y + t * dl.y - cy) / rad),
+                    (float)(((double)ol.z + t * dl.z - cz) / rad));
         } else {
             nl = (pl - c) * inv_r;  // sphere.h:62 — negative radius flips the normal (Q8)
         }
         if (need_uv) sphere_uv(nl, r.u, r.v);
     } else {
-        float4 pb = ld_cold<SM>(&sv.pb[h.prim]);
+        float k = __uint_as_float(cold1<SM>(sv, sc.off[SEC_PB] + (uint32_t)h.prim * 16u));
         float a, b;
         // snap the plane coordinate: in exact arithmetic p lies on the rect (FP32 hygiene against self-hits)
         if (type == RTW_PRIM_XY_RECT) {
-            pl.z = pb.x; a = pl.x; b = pl.y; nl = mk(0.0f, 0.0f, 1.0f);
+            pl.z = k; a = pl.x; b = pl.y; nl = mk(0.0f, 0.0f, 1.0f);
         } else if (type == RTW_PRIM_XZ_RECT) {
-            pl.y = pb.x; a = pl.x; b = pl.z; nl = mk(0.0f, 1.0f, 0.0f);
+            pl.y = k; a = pl.x; b = pl.z; nl = mk(0.0f, 1.0f, 0.0f);
         } else {
-            pl.x = pb.x; a = pl.y; b = pl.z; nl = mk(1.0f, 0.0f, 0.0f);
+            pl.x = k; a = pl.y; b = pl.z; nl = mk(1.0f, 0.0f, 0.0f);
         }
         if (need_uv) {  // hittable.h:158-159
             r.u = (a - pa.x) / (pa.y - pa.x);
@@ -234,14 +252,12 @@ RTW_DEV HitRec complete_hit(const SceneView& sv, const HitId& h, V3 o, V3 d, flo
     if (m & PM_FLIP) nl = -nl;  // hittable.h:277
     if (F & F_XF) {
         if (pxf) {
-            DevXf x = ld_hot<SM>(&sv.xfs[pxf - 1]);
-            nl = xf_vec_out(x, nl);
-            pl = xf_point_out(x, pl);
+            nl = xf_vec_out(xp, nl);
+            pl = xf_point_out(xp, pl);
         }
-        if (ixf >= 0) {
-            DevXf x = ld_hot<SM>(&sv.xfs[ixf]);
-            nl = xf_vec_out(x, nl);
-            pl = xf_point_out(x, pl);
+        if ((F & (F_BVH | F_MEDIA)) && ixf >= 0) {
+            nl = xf_vec_out(xi, nl);
+            pl = xf_point_out(xi, pl);
         }
     }
     r.p = pl;
