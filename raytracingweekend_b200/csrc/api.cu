@@ -2,6 +2,7 @@
 // No CPU fallback: every function here fails with RTW_ERR_CUDA when the CUDA runtime or an sm_100 device
 // is missing.
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -79,11 +80,16 @@ struct rtw_scene {
     int pending_launches = 0;
     float* scratch_accum = nullptr;  // device buffer behind rtw_render (host API)
     size_t scratch_pixels = 0;
+    void* wf_scratch = nullptr;  // wavefront path pool + queues (lazy)
+    uint32_t wf_slots = 0;
+    unsigned long long* wf_host_flag = nullptr;  // pinned
     void release() {
         blob.release();
         texels.release();
         if (d_counter) cudaFree(d_counter);
         if (scratch_accum) cudaFree(scratch_accum);
+        if (wf_scratch) cudaFree(wf_scratch);
+        if (wf_host_flag) cudaFreeHost(wf_host_flag);
         if (ev0) cudaEventDestroy(ev0);
         if (ev1) cudaEventDestroy(ev1);
     }
@@ -420,10 +426,6 @@ extern "C" int rtw_render_device(rtw_scene* s, const rtw_render_params* p, float
         set_error("render: null accumulator");
         return RTW_ERR_INVALID;
     }
-    if (p->flags & RTW_FLAG_WAVEFRONT) {
-        set_error("render: wavefront pipeline not built in this round");
-        return RTW_ERR_UNSUPPORTED;
-    }
     cudaStream_t st = (cudaStream_t)cuda_stream;
     cudaError_t e = cudaSetDevice(s->device);
     if (e != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
@@ -433,11 +435,36 @@ extern "C" int rtw_render_device(rtw_scene* s, const rtw_render_params* p, float
     rp.seed_lo = (uint32_t)(p->seed & 0xffffffffu), rp.seed_hi = (uint32_t)(p->seed >> 32);
     if ((e = cudaMemsetAsync(s->d_counter, 0, sizeof(unsigned long long), st)) != cudaSuccess) return cuda_fail(e, "memset");
     if ((e = cudaEventRecord(s->ev0, st)) != cudaSuccess) return cuda_fail(e, "event");
-    if ((e = launch_render(s->dev, rp, (float4*)accum_dev, s->d_counter, st)) != cudaSuccess) return cuda_fail(e, "render launch");
+    int launches = 1;
+    if (p->flags & RTW_FLAG_WAVEFRONT) {
+        // pool of path slots: L2-resident by default (1 Mi slots = 64 MiB), never larger than the work
+        if (p->max_depth > 255 || (long long)p->spp_begin + p->spp_count >= (1 << 24)) {
+            set_error("render: the wavefront pipeline packs (sample, bounce) into 24+8 bits: max_depth <= 255, samples < 2^24");
+            return RTW_ERR_INVALID;
+        }
+        unsigned long long want = 1ull << 20;
+        if (const char* env = getenv("RTW_WF_SLOTS")) want = strtoull(env, nullptr, 10);
+        unsigned long long paths = (unsigned long long)p->nx * p->ny * p->spp_count;
+        if (want > paths) want = paths;
+        want = (want + 255) & ~255ull;
+        if (want < 256) want = 256;
+        if ((uint32_t)want != s->wf_slots) {
+            if (s->wf_scratch) cudaFree(s->wf_scratch);
+            s->wf_scratch = nullptr, s->wf_slots = 0;
+            if ((e = cudaMalloc(&s->wf_scratch, wavefront_scratch_bytes((uint32_t)want))) != cudaSuccess) return cuda_fail(e, "cudaMalloc wavefront pool");
+            s->wf_slots = (uint32_t)want;
+        }
+        if (!s->wf_host_flag && (e = cudaMallocHost((void**)&s->wf_host_flag, 16)) != cudaSuccess) return cuda_fail(e, "cudaMallocHost");
+        if ((e = launch_wavefront(s->dev, rp, (float4*)accum_dev, s->d_counter, s->wf_scratch, s->wf_slots, s->wf_host_flag, &launches, st)) !=
+            cudaSuccess)
+            return cuda_fail(e, "wavefront launch");
+    } else if ((e = launch_render(s->dev, rp, (float4*)accum_dev, s->d_counter, st)) != cudaSuccess) {
+        return cuda_fail(e, "render launch");
+    }
     if ((e = cudaEventRecord(s->ev1, st)) != cudaSuccess) return cuda_fail(e, "event");
     s->pending = true;
     s->pending_params = *p;
-    s->pending_launches = 1;
+    s->pending_launches = launches;
     return RTW_OK;
 }
 

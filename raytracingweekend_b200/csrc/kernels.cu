@@ -7,6 +7,7 @@
 // the first bounce stay coherent.
 #include "kernels.hpp"
 #include "rt_path.cuh"
+#include "rt_stage.cuh"
 
 namespace rtw {
 
@@ -16,31 +17,6 @@ constexpr int kBlock = 128;   // 4 warps
 #endif
 constexpr int kTileW = 16;    // block tile: 16 x 8 pixels, warp tile 8 x 4
 constexpr int kTileH = 8;
-
-// Stage a prefix of the scene blob into shared memory (16-byte vectors, whole block) and return the view.
-// `sbase` is laundered through an empty volatile asm after the barrier: every staged load depends on it, so none can
-// be scheduled above the barrier, and the compiler keeps it in a register instead of re-deriving the shared window
-// address at each use.
-template <int SM>
-RTW_DEV SceneView stage_scene(const DevScene& sc, uint4* smem) {
-    const uint32_t staged = SM == 2 ? sc.all_bytes : (SM == 1 ? sc.hot_bytes : 0u);
-    if (SM > 0) {
-        const uint4* src = reinterpret_cast<const uint4*>(sc.blob);
-        for (uint32_t i = threadIdx.x; i < staged / 16; i += blockDim.x) smem[i] = __ldg(src + i);
-        __syncthreads();
-    }
-    SceneView v;
-    v.sbase = (uint32_t)__cvta_generic_to_shared(smem);
-    asm volatile("" : "+r"(v.sbase)::"memory");
-    v.g = sc.blob;
-    v.texels = sc.texels;
-    return v;
-}
-// dynamic shared memory: [staged blob prefix][BVH traversal stacks]
-RTW_DEV int* stack_base(const DevScene& sc, int sm_level, uint4* smem) {
-    uint32_t staged = sm_level == 2 ? sc.all_bytes : (sm_level == 1 ? sc.hot_bytes : 0u);
-    return reinterpret_cast<int*>(reinterpret_cast<uint8_t*>(smem) + staged);
-}
 
 template <uint32_t F, int SM>
 __global__ void __launch_bounds__(kBlock, RTW_MIN_BLOCKS) render_megakernel(const __grid_constant__ DevScene sc,
@@ -138,47 +114,9 @@ __global__ void __launch_bounds__(kBlock) intersect_kernel(const __grid_constant
 }
 
 // ------------------------------------------------------------------------------------------------ launchers
-// Kernel specialisations: the smallest feature superset is chosen per scene (registers and code size shrink
-// a lot when BVH / media / textures are compiled out, e.g. for the Cornell box), and the staging level from the
-// blob size: everything in shared memory (<= kStageMax), the hot sections only, or nothing.
-constexpr uint32_t kStageMax = 24 * 1024;  // per block; keeps >= 8 blocks of 128 threads resident per SM
-
-constexpr uint32_t kVariants[] = {
-    F_XF,                                       // Cornell box, dielectric_scene
-    F_XF | F_MOVING | F_PRECISE,                // random_balls_scene
-    F_XF | F_TEXTURES | F_PRECISE,              // light_sample, two_perlin_spheres_earth
-    F_ALL};
-
-uint32_t pick_variant(uint32_t features) {
-    for (uint32_t v : kVariants)
-        if ((features & ~v) == 0) return v;
-    return F_ALL;
-}
-int pick_stage(const DevScene& sc) {
-    if (sc.all_bytes <= kStageMax) return 2;
-    if (sc.hot_bytes <= kStageMax) return 1;
-    return 0;
-}
+uint32_t pick_variant(uint32_t features) { return pick_variant_impl(features); }
 
 namespace {
-struct Launch {
-    uint32_t variant;
-    int stage;
-    size_t smem;
-};
-Launch plan(const DevScene& sc) {
-    Launch l;
-    l.stage = pick_stage(sc);
-    l.variant = pick_variant(sc.features);
-    // instantiated combinations: every variant at stage 2; {moving, all} at stage 1; {all} at stage 0
-    if (l.stage == 1 && l.variant != kVariants[1]) l.variant = F_ALL;
-    if (l.stage == 0) l.variant = F_ALL;
-    size_t staged = l.stage == 2 ? sc.all_bytes : (l.stage == 1 ? sc.hot_bytes : 0);
-    size_t stack = (l.variant & F_BVH) ? (size_t)kStackDepth * kBlock * sizeof(int) : 0;
-    l.smem = staged + stack;
-    return l;
-}
-
 template <uint32_t F, int SM>
 cudaError_t launch_render_t(const DevScene& sc, const DevRenderParams& rp, float4* accum, unsigned long long* counter,
                             size_t smem, cudaStream_t st) {
@@ -203,30 +141,14 @@ cudaError_t launch_intersect_t(const DevScene& sc, const rtw_ray* rays, rtw_hit*
 }
 }  // namespace
 
-#define RTW_DISPATCH(FN, ...)                                                                      \
-    do {                                                                                           \
-        Launch l = plan(sc);                                                                       \
-        if (l.stage == 2) {                                                                        \
-            if (l.variant == kVariants[0]) return FN<kVariants[0], 2>(__VA_ARGS__, l.smem, st);    \
-            if (l.variant == kVariants[1]) return FN<kVariants[1], 2>(__VA_ARGS__, l.smem, st);    \
-            if (l.variant == kVariants[2]) return FN<kVariants[2], 2>(__VA_ARGS__, l.smem, st);    \
-            return FN<F_ALL, 2>(__VA_ARGS__, l.smem, st);                                          \
-        }                                                                                          \
-        if (l.stage == 1) {                                                                        \
-            if (l.variant == kVariants[1]) return FN<kVariants[1], 1>(__VA_ARGS__, l.smem, st);    \
-            return FN<F_ALL, 1>(__VA_ARGS__, l.smem, st);                                          \
-        }                                                                                          \
-        return FN<F_ALL, 0>(__VA_ARGS__, l.smem, st);                                              \
-    } while (0)
-
 cudaError_t launch_render(const DevScene& sc, const DevRenderParams& rp, float4* accum, unsigned long long* counter,
                           cudaStream_t st) {
-    RTW_DISPATCH(launch_render_t, sc, rp, accum, counter);
+    RTW_DISPATCH(kBlock, launch_render_t, sc, rp, accum, counter);
 }
 
 cudaError_t launch_intersect(const DevScene& sc, const rtw_ray* rays, rtw_hit* hits, long long n, float tmin, float tmax,
                              cudaStream_t st) {
-    RTW_DISPATCH(launch_intersect_t, sc, rays, hits, n, tmin, tmax);
+    RTW_DISPATCH(kBlock, launch_intersect_t, sc, rays, hits, n, tmin, tmax);
 }
 
 }  // namespace rtw

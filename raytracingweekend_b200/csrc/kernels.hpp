@@ -16,6 +16,13 @@ cudaError_t launch_render(const DevScene& sc, const DevRenderParams& rp, float4*
 cudaError_t launch_intersect(const DevScene& sc, const rtw_ray* rays, rtw_hit* hits, long long n, float tmin, float tmax,
                              cudaStream_t st);
 
+// Wavefront pipeline (wavefront.cu): generate / extend / shade kernels over a pool of `n_slots` path slots in `scratch`
+// (wavefront_scratch_bytes(n_slots) bytes of device memory).  Synchronises the stream between chunks of iterations to
+// poll the dead-slot counter through `host_flag` (pinned host memory, >= 8 bytes).
+size_t wavefront_scratch_bytes(uint32_t n_slots);
+cudaError_t launch_wavefront(const DevScene& sc, const DevRenderParams& rp, float4* accum, unsigned long long* ray_counter,
+                             void* scratch, uint32_t n_slots, unsigned long long* host_flag, int* launches_out, cudaStream_t st);
+
 // FFMA throughput of the current device in TFLOP/s (roofline denominator, measured not assumed).
 cudaError_t measure_fp32_peak(double* tflops);
 

@@ -10,11 +10,11 @@ namespace rtw {
 
 // Returns true when the path continues with the new `ray`/`beta`; false when it ended (L updated).
 // `bounce` is the 1-based index of this color() invocation (Philox counter word).
+// `shade_hit` is everything of color() after world.hit() (:54-159); `path_step` = world.hit() + shade_hit.  The
+// wavefront pipeline runs the two halves in different kernels.
 template <uint32_t F, int SM>
-RTW_DEV bool path_step(const DevScene& sc, const SceneView& sv, const Rng& rng, uint32_t bounce, Ray& ray, V3& beta, V3& L,
-                       int* stack, int stride) {
-    // :52 world.hit(r, 0.001f, DBL_MAX, rec)
-    HitId h = closest_hit<F, SM, false>(sc, sv, ray.o, ray.d, ray.time, 0.001f, FLT_MAX, &rng, bounce, stack, stride);
+RTW_DEV bool shade_hit(const DevScene& sc, const SceneView& sv, const Rng& rng, uint32_t bounce, const HitId& h, Ray& ray,
+                       V3& beta, V3& L) {
     // The bounce's main uniforms are drawn here, before control flow diverges by material: every lane of the
     // warp runs the ten Philox rounds together instead of once per material branch.
     U4 rmain = rng.draw(bounce, SITE_MAIN);
@@ -112,6 +112,14 @@ RTW_DEV bool path_step(const DevScene& sc, const SceneView& sv, const Rng& rng, 
             return true;
         }
     }
+}
+
+template <uint32_t F, int SM>
+RTW_DEV bool path_step(const DevScene& sc, const SceneView& sv, const Rng& rng, uint32_t bounce, Ray& ray, V3& beta, V3& L,
+                       int* stack, int stride) {
+    // :52 world.hit(r, 0.001f, DBL_MAX, rec)
+    const HitId h = closest_hit<F, SM, false>(sc, sv, ray.o, ray.d, ray.time, 0.001f, FLT_MAX, &rng, bounce, stack, stride);
+    return shade_hit<F, SM>(sc, sv, rng, bounce, h, ray, beta, L);
 }
 
 }  // namespace rtw

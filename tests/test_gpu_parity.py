@@ -214,3 +214,41 @@ def test_device_pointer_api_with_torch(scenes):
     st = sc.finish()
     host, st2 = sc.render(32, 32, 8, seed=9)
     assert np.array_equal(acc.cpu().numpy(), host) and st["rays"] == st2["rays"]
+
+
+@pytest.mark.parametrize("scene,nx,ny,spp", [("cornell_box_aluminum", 96, 64, 16), ("random_balls_scene", 48, 32, 4),
+                                             ("two_perlin_spheres_earth", 40, 40, 8), ("book2_final_scene", 32, 32, 4)])
+def test_wavefront_pipeline_traces_the_same_paths_as_the_megakernel(scenes, scene, nx, ny, spp):
+    """Same device functions, same Philox keys: the wavefront pipeline (generate / extend / shade with ballot compaction)
+    must trace exactly the megakernel's paths — identical ray counts — and the per-pixel sums may differ only by the
+    order of the atomic float adds."""
+    b, sc = scenes(scene, nx / ny)
+    mega, st_m = sc.render(nx, ny, spp, seed=21)
+    wave, st_w = sc.render(nx, ny, spp, seed=21, flags=rtw._lib.RTW_FLAG_WAVEFRONT)
+    assert st_w["rays"] == st_m["rays"] and st_w["paths"] == st_m["paths"]
+    assert st_w["kernel_launches"] > 2
+    assert np.all(wave[..., 3] == spp)
+    fin = np.isfinite(mega).all(axis=2)
+    assert np.array_equal(fin, np.isfinite(wave).all(axis=2))
+    # two separately compiled kernels may contract FP32 expressions differently; a 1-ulp difference in a ray can grow over
+    # a few bounces (without changing the path's topology), so a handful of pixels may differ beyond summation order
+    close = np.isclose(wave, mega, rtol=1e-4, atol=1e-5 * spp).all(axis=2) | ~fin
+    assert close.mean() > 0.995, f"{(~close).sum()} pixels differ"
+    assert np.allclose(wave[fin], mega[fin], rtol=2e-2, atol=1e-3 * spp)
+
+
+def test_wavefront_ragged_shapes_shards_and_accumulate(scenes):
+    b, sc = scenes("cornell_box_aluminum", 1.0)
+    WF = rtw._lib.RTW_FLAG_WAVEFRONT
+    acc, st = sc.render(37, 21, 3, seed=1, flags=WF)  # ragged vs the 8x4 work tiles, fewer paths than one pool
+    ref, st_ref = sc.render(37, 21, 3, seed=1)
+    assert acc.shape == (21, 37, 4) and st["paths"] == 37 * 21 * 3 and st["rays"] == st_ref["rays"]
+    assert np.allclose(acc, ref, rtol=1e-4, atol=1e-4)
+    # spp shards + ACCUMULATE through the wavefront path
+    full, _ = sc.render(64, 64, 16, seed=5)
+    out = np.zeros((64, 64, 4), dtype=np.float32)
+    for g in range(2):
+        sc.render(64, 64, 8, spp_begin=8 * g, seed=5, flags=WF | rtw._lib.RTW_FLAG_ACCUMULATE, out=out)
+    assert np.all(out[..., 3] == 16) and np.allclose(out[..., :3], full[..., :3], rtol=1e-4, atol=1e-4)
+    with pytest.raises(rtw._lib.RtwError):
+        sc.render(8, 8, 1, max_depth=300, flags=WF)

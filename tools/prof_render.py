@@ -1,4 +1,4 @@
-"""Short render loop for ncu captures: `python tools/prof_render.py [scene] [nx] [ny] [spp] [reps]`.
+"""Short render loop for ncu captures: `python tools/prof_render.py [scene] [nx] [ny] [spp] [reps] [flags]`.
 
 Same kernel and launch shape as bench.py's step, but with few samples so that ncu's ~40 replays stay cheap.
 """
@@ -13,8 +13,10 @@ nx = int(sys.argv[2]) if len(sys.argv) > 2 else 1024
 ny = int(sys.argv[3]) if len(sys.argv) > 3 else 1024
 spp = int(sys.argv[4]) if len(sys.argv) > 4 else 64
 reps = int(sys.argv[5]) if len(sys.argv) > 5 else 4
+flags = int(sys.argv[6]) if len(sys.argv) > 6 else 0  # 1 = RTW_FLAG_WAVEFRONT
 sc = r.Scene.named(name, nx / ny)
+tag = " [wavefront]" if flags & 1 else ""
 for _ in range(reps):
-    acc, st = sc.render(nx, ny, spp)
-    print(f"{name} {nx}x{ny}x{spp}: kernel_ms={st['kernel_ms']:.2f} Gpaths/s={st['paths'] / st['kernel_ms'] / 1e6:.3f} "
+    acc, st = sc.render(nx, ny, spp, flags=flags)
+    print(f"{name}{tag} {nx}x{ny}x{spp}: launches={st['kernel_launches']} kernel_ms={st['kernel_ms']:.2f} Gpaths/s={st['paths'] / st['kernel_ms'] / 1e6:.3f} "
           f"Grays/s={st['rays'] / st['kernel_ms'] / 1e6:.3f}", flush=True)
