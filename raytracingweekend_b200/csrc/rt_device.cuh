@@ -249,13 +249,16 @@ RTW_DEV void rect_update(float4 ra, float k, int id, float on, float inv_n, floa
                          float& t_best, int& prim_best) {
     float t = (k - on) * inv_n;
     float a = fmaf(t, da, oa), b = fmaf(t, db, ob);
-    asm("{\n\t.reg .pred p;\n\t"
+    // two independent 3-deep predicate chains (t range + first axis | second axis) joined at the end: one more
+    // instruction than a single 6-deep chain, half the dependent latency
+    asm("{\n\t.reg .pred p, q;\n\t"
         "setp.lt.ftz.f32 p, %2, %4;\n\t"
+        "setp.lt.ftz.f32 q, %5, %7;\n\t"
         "setp.gt.or.ftz.f32 p, %2, %0, p;\n\t"
-        "setp.lt.or.ftz.f32 p, %5, %7, p;\n\t"
-        "setp.gt.or.ftz.f32 p, %5, %8, p;\n\t"
+        "setp.gt.or.ftz.f32 q, %5, %8, q;\n\t"
         "setp.lt.or.ftz.f32 p, %6, %9, p;\n\t"
-        "setp.gt.or.ftz.f32 p, %6, %10, p;\n\t"
+        "setp.gt.or.ftz.f32 q, %6, %10, q;\n\t"
+        "or.pred p, p, q;\n\t"
         "@!p mov.f32 %0, %2;\n\t"
         "@!p mov.b32 %1, %3;\n\t}"
         : "+f"(t_best), "+r"(prim_best)
