@@ -219,31 +219,52 @@ def run_ours(args) -> None:
     value = paths_per_step * args.steps / (total_ms * 1e-3)
     rays_per_s = total_rays / (total_ms * 1e-3)
 
+    # ---- end to end through the public API with HOST buffers, at N GPUs, every step from scratch:
+    #      scene description -> flatten -> H2D upload -> render (this rank's sample shard) -> [ncclReduce to rank 0] ->
+    #      D2H of the float4 image into pinned host memory on rank 0.  Wall clock between barriers, max over ranks.
+    #      N = 1 goes through the C-ABI host-buffer call rtw_render itself (Scene.render).
+    import ctypes as C
+    from raytracingweekend_b200.dist import render_sharded
+    fs = builder.flatten().contents
+    h2d = (fs.n_items * 32 + fs.n_prims * 36 + fs.n_xfs * 32 + fs.n_nodes * 32 + fs.n_leaves * 8 + fs.n_materials * 32 +
+           fs.n_textures * 48 + fs.n_lights * 32 + fs.n_texel_bytes + C.sizeof(_lib.RenderParams))
+    host_t = torch.empty((NY, NX, 4), dtype=torch.float32).pin_memory()
+    host = host_t.numpy()
+    e2e_steps = max(1, min(args.steps, 3))
+    e2e_times = []
+    for _ in range(e2e_steps):
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        b2 = rtw.Builder().named_scene(SCENE, NX / NY)   # scene description -> flatten
+        s2 = rtw.Scene(b2, device=local)                 # H2D upload of the flat arrays
+        if world == 1:
+            s2.render(NX, NY, SPP, max_depth=MAX_DEPTH, seed=0, out=host)  # kernel + D2H of the float4 image
+        else:
+            acc2, _ = render_sharded(s2, NX, NY, SPP, max_depth=MAX_DEPTH, seed=0, accum=accum)  # shard + ncclReduce
+            if rank == 0:
+                host_t.copy_(acc2, non_blocking=False)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        s2.close()
+        b2.close()
+        e2e_times.append(dt)
+    te = torch.tensor([sum(e2e_times)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_s = float(te[0]) / e2e_steps
+
     if rank != 0:
         if world > 1:
             dist.barrier()
             dist.destroy_process_group()
         return
-
-    # ---- end to end through the public host-buffer call (rank 0's GPU; at N > 1 this is still the 1-GPU call) ----
-    fs = builder.flatten().contents
-    import ctypes as C
-    h2d = (fs.n_items * 32 + fs.n_prims * 36 + fs.n_xfs * 32 + fs.n_nodes * 32 + fs.n_leaves * 8 + fs.n_materials * 32 +
-           fs.n_textures * 48 + fs.n_lights * 32 + fs.n_texel_bytes + C.sizeof(_lib.RenderParams))
-    host = np.empty((NY, NX, 4), dtype=np.float32)
-    e2e_steps = max(1, min(args.steps, 3))
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        b2 = rtw.Builder().named_scene(SCENE, NX / NY)   # scene description -> flatten
-        s2 = rtw.Scene(b2, device=local)                 # H2D upload of the flat arrays
-        s2.render(NX, NY, SPP, max_depth=MAX_DEPTH, seed=0, out=host)  # kernel + D2H of the float4 image
-        s2.close()
-        b2.close()
-    e2e_s = (time.perf_counter() - t0) / e2e_steps
-    e2e = {"value": paths_per_step / e2e_s, "unit": "paths/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": NX * NY * 16,
-           "ms_per_step": e2e_s * 1e3, "n_gpus": 1,
-           "what": "Builder.named_scene + Scene() + rtw_render into a host buffer (flatten, H2D, kernel, D2H)"}
+    e2e = {"value": paths_per_step / e2e_s, "unit": "paths/s", "h2d_bytes_per_step": int(h2d) * world,
+           "d2h_bytes_per_step": NX * NY * 16, "ms_per_step": e2e_s * 1e3, "n_gpus": world,
+           "what": ("Builder.named_scene + Scene() + rtw_render into a host buffer (flatten, H2D, kernel, D2H)" if world == 1 else
+                    "per rank: Builder.named_scene + Scene() + rtw_render_device of its sample shard; ncclReduce to rank 0; "
+                    "D2H of the image into pinned host memory")}
 
     # ---- roofline: FP32 issue ----
     peak = C.c_double(0)
