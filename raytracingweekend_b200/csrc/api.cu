@@ -1,7 +1,10 @@
 // api.cu — device scene upload + the hot-path entry points of include/rtw_b200.h.
 // No CPU fallback: every function here fails with RTW_ERR_CUDA when the CUDA runtime or an sm_100 device
 // is missing.
+#include <algorithm>
 #include <cmath>
+#include <functional>
+#include <limits>
 #include <cstdlib>
 #include <cstring>
 #include <string>
@@ -50,6 +53,40 @@ void compose_chain(const rtw_flat_scene* fs, int head, DevXf& out) {
     }
     out = DevXf{(float)C, (float)S, (float)t[0], (float)t[1], (float)t[2], 0, 0, 0};
 }
+
+// Composition in FP64 (bounding boxes): local = Ry(o) + t with Ry: x' = C x - S z, z' = S x + C z.
+void compose_chain_f64(const rtw_flat_scene* fs, int head, double& C, double& S, double t[3]) {
+    C = 1, S = 0, t[0] = t[1] = t[2] = 0;
+    for (int i = head; i >= 0; i = fs->xfs[i].next) {
+        const rtw_flat_xf& x = fs->xfs[i];
+        if (x.kind == RTW_XF_TRANSLATE) {
+            t[0] -= x.a, t[1] -= x.b, t[2] -= x.c;
+        } else {
+            double s = x.a, c = x.b;
+            double nC = c * C - s * S, nS = s * C + c * S;
+            double tx = c * t[0] - s * t[2], tz = s * t[0] + c * t[2];
+            C = nC, S = nS, t[0] = tx, t[2] = tz;
+        }
+    }
+}
+
+struct Box {
+    double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+    void grow_axis(int k, double a, double b) {
+        lo[k] = std::min(lo[k], std::min(a, b));
+        hi[k] = std::max(hi[k], std::max(a, b));
+    }
+    void grow_point(double x, double y, double z) { grow_axis(0, x, x), grow_axis(1, y, y), grow_axis(2, z, z); }
+    void merge(const Box& o) {
+        for (int k = 0; k < 3; k++) lo[k] = std::min(lo[k], o.lo[k]), hi[k] = std::max(hi[k], o.hi[k]);
+    }
+    double centre(int k) const { return 0.5 * (lo[k] + hi[k]); }
+    double area() const {
+        if (hi[0] < lo[0]) return 0.0;
+        double x = hi[0] - lo[0], y = hi[1] - lo[1], z = hi[2] - lo[2];
+        return 2.0 * (x * y + y * z + z * x);
+    }
+};
 
 inline float __int_as_float_host(int v) {
     float f;
@@ -176,24 +213,25 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
         pm[i] = m;
     }
 
-    // primitive-test groups and records (device_scene.hpp): split a run of primitives into maximal runs that
-    // share a transform chain, and order each run's records spheres, moving spheres, xy, xz, yz rects.
+    // primitive-test groups and records (device_scene.hpp): split a set of primitives (ascending list order) into maximal
+    // runs that share a transform chain, and order each run's records spheres, moving spheres, xy, xz, yz rects.
     // Built with INDICES first; converted to blob byte offsets once the section offsets are known (below).
     std::vector<DevGroup> groups;
     std::vector<DevRec> recs;
-    auto add_groups = [&](int first, int count, int& first_group, int& end_group) {
+    auto add_groups_of = [&](const std::vector<int>& ids, int& first_group, int& end_group) {
         first_group = (int)groups.size();
-        int i = first;
-        while (i < first + count) {
-            int j = i;
-            while (j < first + count && fs->prims[j].xf == fs->prims[i].xf) j++;
+        size_t i = 0;
+        while (i < ids.size()) {
+            size_t j = i;
+            while (j < ids.size() && fs->prims[ids[j]].xf == fs->prims[ids[i]].xf) j++;
             DevGroup g{};
-            g.xf = fs->prims[i].xf;
+            g.xf = fs->prims[ids[i]].xf;
             g.sph0 = (int)recs.size();
             const int kinds[5] = {RTW_PRIM_SPHERE, RTW_PRIM_MOVING_SPHERE, RTW_PRIM_XY_RECT, RTW_PRIM_XZ_RECT, RTW_PRIM_YZ_RECT};
             int32_t* ends[5] = {&g.sph1, &g.msph1, &g.xy1, &g.xz1, &g.yz1};
             for (int k = 0; k < 5; k++) {
-                for (int p = i; p < j; p++) {
+                for (size_t q = i; q < j; q++) {
+                    const int p = ids[q];
                     if (fs->prims[p].type != kinds[k]) continue;
                     DevRec r{};
                     r.a = pa[p];
@@ -218,9 +256,215 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
         }
         end_group = (int)groups.size();
     };
+    auto add_groups = [&](int first, int count, int& first_group, int& end_group) {
+        std::vector<int> ids(count);
+        for (int k = 0; k < count; k++) ids[k] = first + k;
+        add_groups_of(ids, first_group, end_group);
+    };
+
+    // ---- bounding boxes (FP64, in the frame the primitive's own chain starts from), padded for FP32 slab tests -----------
+    const double cam_t0 = fs->camera.time0, cam_t1 = fs->camera.time1;
+    auto prim_box = [&](int p) {
+        const rtw_flat_prim& pr = fs->prims[p];
+        Box b;
+        const double* v = pr.v;
+        if (pr.type == RTW_PRIM_SPHERE) {
+            double r = std::fabs(v[3]);
+            for (int k = 0; k < 3; k++) b.grow_axis(k, v[k] - r, v[k] + r);
+        } else if (pr.type == RTW_PRIM_MOVING_SPHERE) {  // sphere.h:22-25 at both ends of the shutter interval
+            double r = std::fabs(v[3]), mt0 = v[7], mt1 = v[8];
+            for (double tm : {cam_t0, cam_t1}) {
+                double f = (tm - mt0) / (mt1 - mt0);
+                for (int k = 0; k < 3; k++) {
+                    double c = v[k] + f * (v[4 + k] - v[k]);
+                    b.grow_axis(k, c - r, c + r);
+                }
+            }
+        } else {
+            const double e = 0.0001;  // hittable.h:169
+            int ax[3];  // in-plane axes a, b and the normal axis
+            if (pr.type == RTW_PRIM_XY_RECT) ax[0] = 0, ax[1] = 1, ax[2] = 2;
+            else if (pr.type == RTW_PRIM_XZ_RECT) ax[0] = 0, ax[1] = 2, ax[2] = 1;
+            else ax[0] = 1, ax[1] = 2, ax[2] = 0;
+            b.grow_axis(ax[0], v[0], v[1]), b.grow_axis(ax[1], v[2], v[3]), b.grow_axis(ax[2], v[4] - e, v[4] + e);
+        }
+        if (pr.xf >= 0) {  // local = Ry(outer) + t  ->  outer = Ry^-1(local - t)
+            double C, S, t[3];
+            compose_chain_f64(fs, pr.xf, C, S, t);
+            Box w;
+            for (int c = 0; c < 8; c++) {
+                double lx = ((c & 1) ? b.hi[0] : b.lo[0]) - t[0], ly = ((c & 2) ? b.hi[1] : b.lo[1]) - t[1],
+                       lz = ((c & 4) ? b.hi[2] : b.lo[2]) - t[2];
+                w.grow_point(C * lx + S * lz, ly, -S * lx + C * lz);
+            }
+            b = w;
+        }
+        return b;
+    };
+    auto padded = [](Box b) {
+        for (int k = 0; k < 3; k++) {
+            double m = std::max(std::fabs(b.lo[k]), std::fabs(b.hi[k]));
+            double pad = 1e-3 + 2e-5 * m;
+            b.lo[k] -= pad, b.hi[k] += pad;
+        }
+        return b;
+    };
+
+    // ---- traversal nodes ---------------------------------------------------------------------------------------------------
+    std::vector<DevNode> nodes;
+    std::vector<int2> leaves;
+    std::vector<Box> leaf_box;
+    const float kInf = std::numeric_limits<float>::infinity();
+    auto set_child = [&](DevNode& n, bool right, const Box* b, int ref) {
+        float4 lo = make_float4(kInf, kInf, kInf, 0.0f), hi = make_float4(-kInf, -kInf, -kInf, 0.0f);  // empty: never hit
+        if (b) {
+            // round outwards so the FP32 box contains the FP64 one
+            lo = make_float4(std::nextafterf((float)b->lo[0], -kInf), std::nextafterf((float)b->lo[1], -kInf),
+                             std::nextafterf((float)b->lo[2], -kInf), 0.0f);
+            hi = make_float4(std::nextafterf((float)b->hi[0], kInf), std::nextafterf((float)b->hi[1], kInf),
+                             std::nextafterf((float)b->hi[2], kInf), 0.0f);
+        }
+        if (right) {
+            n.rlo = lo, n.rhi = hi;
+            n.lhi.w = __int_as_float_host(ref);
+        } else {
+            n.llo.x = lo.x, n.llo.y = lo.y, n.llo.z = lo.z, n.llo.w = __int_as_float_host(ref);
+            n.lhi.x = hi.x, n.lhi.y = hi.y, n.lhi.z = hi.z;
+        }
+    };
+    auto exact_child = [&](DevNode& n, bool right, const double* bmin, const double* bmax, int ref) {
+        // a reference bvh_node's own box, converted like every other scene constant (round to nearest)
+        float4 lo = make_float4((float)bmin[0], (float)bmin[1], (float)bmin[2], 0.0f);
+        float4 hi = make_float4((float)bmax[0], (float)bmax[1], (float)bmax[2], 0.0f);
+        if (right) {
+            n.rlo = lo, n.rhi = hi;
+            n.lhi.w = __int_as_float_host(ref);
+        } else {
+            n.llo.x = lo.x, n.llo.y = lo.y, n.llo.z = lo.z, n.llo.w = __int_as_float_host(ref);
+            n.lhi.x = hi.x, n.lhi.y = hi.y, n.lhi.z = hi.z;
+        }
+    };
+
+    // (1) the reference's bvh_node trees, same topology: node i of the flat scene is device node i
+    nodes.resize(fs->n_nodes);
+    leaves.resize(fs->n_leaves);
+    leaf_box.resize(fs->n_leaves);
+    for (int i = 0; i < fs->n_leaves; i++) {
+        add_groups(fs->leaves[i].first_prim, fs->leaves[i].prim_count, leaves[i].x, leaves[i].y);
+        Box b;
+        for (int p = 0; p < fs->leaves[i].prim_count; p++) b.merge(prim_box(fs->leaves[i].first_prim + p));
+        leaf_box[i] = padded(b);
+    }
+    for (int i = 0; i < fs->n_nodes; i++) {
+        const rtw_flat_node& n = fs->nodes[i];
+        DevNode d{};
+        for (int side = 0; side < 2; side++) {
+            int ref = side ? n.right : n.left;
+            if (side && n.right == n.left) {  // n == 1 (hittable.h:68-72): one visit is enough
+                set_child(d, true, nullptr, ref);
+            } else if (ref >= 0) {
+                exact_child(d, side, fs->nodes[ref].bmin, fs->nodes[ref].bmax, ref);
+            } else {
+                set_child(d, side, &leaf_box[~ref], ref);
+            }
+        }
+        nodes[i] = d;
+    }
+
+    // (2) trees built here over long hittable_lists (hittable_list.h:11-37 walks them linearly; the closest hit is the
+    // same, the reference's order-dependent tie rules only matter for bit-equal t of different primitives)
+    int list_bvh_min = 32;
+    if (const char* env = getenv("RTW_LIST_BVH_MIN")) list_bvh_min = atoi(env);
+    int max_depth = 0;
+    std::function<int(std::vector<int>&, int)> build_list = [&](std::vector<int>& ids, int depth) -> int {
+        if (depth > max_depth) max_depth = depth;
+        auto make_leaf = [&](std::vector<int>& leaf_ids) {
+            std::sort(leaf_ids.begin(), leaf_ids.end());  // list order inside the leaf
+            int2 lf;
+            add_groups_of(leaf_ids, lf.x, lf.y);
+            Box b;
+            for (int p : leaf_ids) b.merge(prim_box(p));
+            leaves.push_back(lf);
+            leaf_box.push_back(padded(b));
+            return ~(int)(leaves.size() - 1);
+        };
+        if (ids.size() <= 2) return make_leaf(ids);
+        // binned SAH on centroids (16 bins, 3 axes)
+        Box cb;
+        std::vector<Box> pbx(ids.size());
+        for (size_t k = 0; k < ids.size(); k++) {
+            pbx[k] = prim_box(ids[k]);
+            cb.grow_point(pbx[k].centre(0), pbx[k].centre(1), pbx[k].centre(2));
+        }
+        double best_cost = 1e300;
+        int best_axis = -1, best_bin = 0;
+        const int NB = 16;
+        for (int ax = 0; ax < 3; ax++) {
+            double lo = cb.lo[ax], ext = cb.hi[ax] - cb.lo[ax];
+            if (!(ext > 1e-12)) continue;
+            Box bb[NB];
+            int cnt[NB] = {};
+            for (size_t k = 0; k < ids.size(); k++) {
+                int bi = std::min(NB - 1, (int)((pbx[k].centre(ax) - lo) / ext * NB));
+                bb[bi].merge(pbx[k]);
+                cnt[bi]++;
+            }
+            Box lb[NB], rb[NB];
+            int lc[NB], rc[NB];
+            Box acc;
+            int c = 0;
+            for (int k = 0; k < NB; k++) acc.merge(bb[k]), c += cnt[k], lb[k] = acc, lc[k] = c;
+            acc = Box(), c = 0;
+            for (int k = NB - 1; k >= 0; k--) acc.merge(bb[k]), c += cnt[k], rb[k] = acc, rc[k] = c;
+            for (int k = 0; k + 1 < NB; k++) {
+                if (!lc[k] || !rc[k + 1]) continue;
+                double cost = lb[k].area() * lc[k] + rb[k + 1].area() * rc[k + 1];
+                if (cost < best_cost) best_cost = cost, best_axis = ax, best_bin = k;
+            }
+        }
+        std::vector<int> L, R;
+        if (best_axis >= 0) {
+            double lo = cb.lo[best_axis], ext = cb.hi[best_axis] - cb.lo[best_axis];
+            for (size_t k = 0; k < ids.size(); k++) {
+                int bi = std::min(NB - 1, (int)((pbx[k].centre(best_axis) - lo) / ext * NB));
+                (bi <= best_bin ? L : R).push_back(ids[k]);
+            }
+        }
+        if (L.empty() || R.empty()) {  // coincident centroids: split in list order
+            L.assign(ids.begin(), ids.begin() + ids.size() / 2);
+            R.assign(ids.begin() + ids.size() / 2, ids.end());
+        }
+        // leaves of up to 4 primitives when splitting further does not pay (SAH with node cost ~ 2 primitive tests)
+        if (ids.size() <= 4) {
+            Box all;
+            for (auto& b : pbx) all.merge(b);
+            Box lbx, rbx;
+            for (int p : L) lbx.merge(prim_box(p));
+            for (int p : R) rbx.merge(prim_box(p));
+            double split_cost = 2.0 + (lbx.area() * L.size() + rbx.area() * R.size()) / std::max(all.area(), 1e-300);
+            if (split_cost >= (double)ids.size()) return make_leaf(ids);
+        }
+        int idx = (int)nodes.size();
+        nodes.push_back(DevNode{});
+        int lref = build_list(L, depth + 1), rref = build_list(R, depth + 1);
+        DevNode d{};
+        auto child_box = [&](int ref) {
+            if (ref < 0) return leaf_box[~ref];
+            Box b;  // union of the child's two child boxes (already padded and rounded outwards)
+            const DevNode& c = nodes[ref];
+            b.grow_point(c.llo.x, c.llo.y, c.llo.z), b.grow_point(c.lhi.x, c.lhi.y, c.lhi.z);
+            if (c.rlo.x <= c.rhi.x) b.grow_point(c.rlo.x, c.rlo.y, c.rlo.z), b.grow_point(c.rhi.x, c.rhi.y, c.rhi.z);
+            return b;
+        };
+        Box lb = child_box(lref), rb = child_box(rref);
+        set_child(d, false, &lb, lref);
+        set_child(d, true, &rb, rref);
+        nodes[idx] = d;
+        return idx;
+    };
 
     std::vector<DevItem> items(fs->n_items);
-    int max_depth = 0;
+    std::vector<std::pair<int, Box>> roots;  // (item, root box) of every tree: pseudo-roots are appended below
     for (int i = 0; i < fs->n_items; i++) {
         const rtw_flat_item& it = fs->items[i];
         DevItem d{};
@@ -231,25 +475,42 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
             feat |= F_BVH;
             int dep = bvh_depth(fs, it.first, 0);
             if (dep > max_depth) max_depth = dep;
+            DevNode pr{};
+            exact_child(pr, false, fs->nodes[it.first].bmin, fs->nodes[it.first].bmax, it.first);
+            set_child(pr, true, nullptr, it.first);
+            d.first = (int)nodes.size();
+            nodes.push_back(pr);
+        } else if (it.type == RTW_ITEM_PRIMS && list_bvh_min > 0 && it.count >= list_bvh_min) {
+            feat |= F_BVH;
+            std::vector<int> ids(it.count);
+            for (int k = 0; k < it.count; k++) ids[k] = it.first + k;
+            int root = build_list(ids, 1);
+            DevNode pr{};
+            Box rb;
+            if (root >= 0) {
+                const DevNode& c = nodes[root];
+                rb.grow_point(c.llo.x, c.llo.y, c.llo.z), rb.grow_point(c.lhi.x, c.lhi.y, c.lhi.z);
+                if (c.rlo.x <= c.rhi.x) rb.grow_point(c.rlo.x, c.rlo.y, c.rlo.z), rb.grow_point(c.rhi.x, c.rhi.y, c.rhi.z);
+            } else {
+                rb = leaf_box[~root];
+            }
+            set_child(pr, false, &rb, root);
+            set_child(pr, true, nullptr, root);
+            d.type = RTW_ITEM_BVH;
+            d.first = (int)nodes.size();
+            d.end = 0;
+            nodes.push_back(pr);
         } else {
             add_groups(it.first, it.count, d.first, d.end);
         }
         if (it.type == RTW_ITEM_MEDIUM) feat |= F_MEDIA;
         items[i] = d;
     }
-    if (max_depth > 30) {
-        set_error("scene_create: bvh deeper than the 32-entry traversal stack");
+    max_depth += 1;  // pseudo-root
+    if (max_depth > 60) {
+        set_error("scene_create: bvh deeper than the 62-entry traversal stack");
         return nullptr;
     }
-
-    std::vector<DevNode> nodes(fs->n_nodes);
-    for (int i = 0; i < fs->n_nodes; i++) {
-        const rtw_flat_node& n = fs->nodes[i];
-        nodes[i].lo = make_float4((float)n.bmin[0], (float)n.bmin[1], (float)n.bmin[2], __int_as_float_host(n.left));
-        nodes[i].hi = make_float4((float)n.bmax[0], (float)n.bmax[1], (float)n.bmax[2], __int_as_float_host(n.right));
-    }
-    std::vector<int2> leaves(fs->n_leaves);
-    for (int i = 0; i < fs->n_leaves; i++) add_groups(fs->leaves[i].first_prim, fs->leaves[i].prim_count, leaves[i].x, leaves[i].y);
 
     std::vector<DevTex> texs(fs->n_textures);
     for (int i = 0; i < fs->n_textures; i++) {
@@ -340,8 +601,8 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
     }
     for (DevNode& n : nodes) {
         int l, r;
-        memcpy(&l, &n.lo.w, 4), memcpy(&r, &n.hi.w, 4);
-        n.lo.w = __int_as_float_host(ref_off(l)), n.hi.w = __int_as_float_host(ref_off(r));
+        memcpy(&l, &n.llo.w, 4), memcpy(&r, &n.lhi.w, 4);
+        n.llo.w = __int_as_float_host(ref_off(l)), n.lhi.w = __int_as_float_host(ref_off(r));
     }
     for (int2& lf : leaves) lf.x = group_off(lf.x), lf.y = group_off(lf.y);
     auto pd_off = [&](float idx_bits) {

@@ -66,11 +66,22 @@ struct DevRec {
 };
 constexpr int32_t REC_PRECISE = 1 << 30;
 
-// bvh_node (hittable.h:137-139), 32 bytes.  Child references: >= 0 byte offset of a DevNode; < 0: ~(byte offset of
-// the leaf's int2 {first group offset, end group offset}).
+// One traversal step of a bounding-volume tree, 64 bytes: the boxes of BOTH children live in the parent, so one visit
+// decides both (bvh_node::hit, hittable.h:97-129, enters a child iff the child's own box is hit — the same boxes, tested
+// one level up).  Child references: >= 0 byte offset of a DevNode; < 0: ~(byte offset of the leaf's int2 {first group
+// offset, end group offset}).  Leaves are numbered left to right, so the byte offset orders them as the tree does.
+//   * a reference bvh_node child keeps the reference's box (hittable.h:84-94);
+//   * a LEAF child (a list/box/primitive — the reference calls its hit() without any box test) carries a padded
+//     bounding box of its primitives, so most leaves are skipped without touching their records: a ray that hits a
+//     primitive passes through its padded box, so no hit is ever lost;
+//   * a node with left == right (n == 1, hittable.h:68-72) has an empty right box: one visit;
+//   * every tree gets a pseudo-root whose left child is the real root (with the root's own box) and whose right box is empty.
+// The same structure backs the trees this backend builds itself over long hittable_lists (api.cu build_list_bvh).
 struct DevNode {
-    float4 lo;  // bmin.xyz, left reference (int bits)
-    float4 hi;  // bmax.xyz, right reference (int bits)
+    float4 llo;  // left child box min.xyz, left reference (int bits)
+    float4 lhi;  // left child box max.xyz, right reference (int bits)
+    float4 rlo;  // right child box min.xyz
+    float4 rhi;  // right child box max.xyz
 };
 
 struct DevMat {

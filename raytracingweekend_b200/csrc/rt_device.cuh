@@ -266,29 +266,32 @@ RTW_DEV void rect_update(float4 ra, float k, int id, float on, float inv_n, floa
 }
 
 // aabb::hit (aabb.h:17-47) with std::max/std::min written out so NaN behaves as in the reference (Q32).
-RTW_DEV bool aabb_hit(float4 lo, float4 hi, V3 o, V3 inv, float tmin, float tmax) {
+// `t_entry` = the interval's lower end after the three slabs (orders the two children of a node).
+RTW_DEV bool aabb_hit(float4 lo, float4 hi, V3 o, V3 inv, float tmin, float tmax, float& t_entry) {
+    bool ok;
     {
         float t0 = (lo.x - o.x) * inv.x, t1 = (hi.x - o.x) * inv.x;
         if (inv.x < 0.0f) { float s = t0; t0 = t1; t1 = s; }
         tmin = (t0 < tmin) ? tmin : t0;
         tmax = (tmax < t1) ? tmax : t1;
-        if (tmax <= tmin) return false;
+        ok = !(tmax <= tmin);
     }
     {
         float t0 = (lo.y - o.y) * inv.y, t1 = (hi.y - o.y) * inv.y;
         if (inv.y < 0.0f) { float s = t0; t0 = t1; t1 = s; }
         tmin = (t0 < tmin) ? tmin : t0;
         tmax = (tmax < t1) ? tmax : t1;
-        if (tmax <= tmin) return false;
+        ok = ok & !(tmax <= tmin);
     }
     {
         float t0 = (lo.z - o.z) * inv.z, t1 = (hi.z - o.z) * inv.z;
         if (inv.z < 0.0f) { float s = t0; t0 = t1; t1 = s; }
         tmin = (t0 < tmin) ? tmin : t0;
         tmax = (tmax < t1) ? tmax : t1;
-        if (tmax <= tmin) return false;
+        ok = ok & !(tmax <= tmin);
     }
-    return true;
+    t_entry = tmin;
+    return ok;
 }
 
 // ------------------------------------------------------------------------------------------------ closest hit

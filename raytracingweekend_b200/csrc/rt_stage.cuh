@@ -40,7 +40,7 @@ constexpr uint32_t kStageMax = 24 * 1024;  // per block; keeps >= 8 blocks of 12
 
 constexpr uint32_t kVariants[] = {
     F_XF,                                       // Cornell box, dielectric_scene
-    F_XF | F_MOVING | F_PRECISE,                // random_balls_scene
+    F_XF | F_MOVING | F_PRECISE | F_BVH,        // random_balls_scene (485-sphere list under a tree built at upload)
     F_XF | F_TEXTURES | F_PRECISE,              // light_sample, two_perlin_spheres_earth
     F_ALL};
 
@@ -65,11 +65,10 @@ inline Launch plan(const DevScene& sc, int block) {
     Launch l;
     l.stage = pick_stage(sc);
     l.variant = pick_variant_impl(sc.features);
-    // instantiated combinations: every variant at stage 2; {moving, all} at stage 1; {all} at stage 0
-    if (l.stage == 1 && l.variant != kVariants[1]) l.variant = F_ALL;
-    if (l.stage == 0) l.variant = F_ALL;
+    // instantiated combinations: every variant at stage 2; {moving, all} at stages 1 and 0
+    if (l.stage < 2 && l.variant != kVariants[1]) l.variant = F_ALL;
     size_t staged = l.stage == 2 ? sc.all_bytes : (l.stage == 1 ? sc.hot_bytes : 0);
-    size_t stack = (l.variant & F_BVH) ? (size_t)kStackDepth * block * sizeof(int) : 0;
+    size_t stack = (l.variant & F_BVH) ? (size_t)(sc.max_bvh_depth + 2) * block * sizeof(int) : 0;
     l.smem = staged + stack;
     return l;
 }
@@ -89,5 +88,6 @@ inline Launch plan(const DevScene& sc, int block) {
             if (l.variant == kVariants[1]) return FN<kVariants[1], 1>(__VA_ARGS__, l.smem, st);    \
             return FN<F_ALL, 1>(__VA_ARGS__, l.smem, st);                                          \
         }                                                                                          \
+        if (l.variant == kVariants[1]) return FN<kVariants[1], 0>(__VA_ARGS__, l.smem, st);        \
         return FN<F_ALL, 0>(__VA_ARGS__, l.smem, st);                                              \
     } while (0)

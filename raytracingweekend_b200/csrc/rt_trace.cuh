@@ -4,50 +4,70 @@
 
 namespace rtw {
 
-constexpr int kStackDepth = 32;  // shared-memory traversal stack entries per thread
-
-// bvh_node::hit (hittable.h:97-129, as intended — SURVEY F1).  A node is entered iff its box passes
-// aabb::hit with the caller's [tmin, tmax]; both children are then examined; the smaller t wins and on equal t
-// the right (later) subtree wins (:107).  Leaves are lists (a box is six rects) evaluated with list semantics
-// against the caller's tmax.  The interval used for box culling shrinks to the best hit found so far, widened
-// by a relative margin that covers the 1/d-multiply vs divide rounding gap, so no candidate with
-// t <= best is ever culled and the winner is the reference's.
-// Stack: shared memory, one column per thread (`stack[level * stride]`), depth-first, left first.
-// References are byte offsets (DevNode): >= 0 node, < 0 ~leaf.
+// bvh_node::hit (hittable.h:97-129, as intended — SURVEY F1).  A node is entered iff its box passes aabb::hit with the
+// caller's [tmin, tmax]; both children are then examined; the smaller t wins and on equal t the right (later) subtree
+// wins (:107).  Leaves are lists (a box is six rects) evaluated with list semantics against the caller's tmax.
+//
+// Device form (DevNode, device_scene.hpp): both child boxes are tested at the parent; the nearer child is descended
+// first and the farther one pushed; the interval used for box culling shrinks to the best hit found so far, widened by
+// a relative margin that covers the 1/d-multiply vs divide rounding gap, so no candidate with t <= best is ever culled.
+// Because the visiting order is no longer left-to-right, the reference's tie rule is applied explicitly: among equal t
+// the leaf further right in the tree (larger leaf offset) wins.
+// The loop is "while-while": every lane first descends inner nodes until it holds a leaf, then all lanes of the warp
+// that hold one test their leaves together, so node steps and primitive tests do not serialise against each other.
+// Stack: shared memory, one column per thread (`stack[level * stride]`).
+constexpr int kBvhDone = (int)0x80000000;  // not a valid reference: ~0x7fffffff is never a leaf offset
 template <uint32_t F, int SM, bool SHRINK>
 RTW_DEV void bvh_hit(const SceneView& sv, int root, const RayK& rk, float time, float tmin, float tmax, int* stack,
                      int stride, float& t_out, int& prim_out) {
     const V3 o = rk.o, inv = rk.inv;
     float best = tmax;
-    int best_prim = -1;
+    int best_prim = -1, best_leaf = 0;
     int sp = 0;
     int ref = root;
     for (;;) {
-        if (ref >= 0) {
-            float4 lo = hot4<SM>(sv, (uint32_t)ref), hi = hot4<SM>(sv, (uint32_t)ref + 16);
-            float cull = (SHRINK && best_prim >= 0) ? fmaf(best, 4e-6f, best) : tmax;
-            if (aabb_hit(lo, hi, o, inv, tmin, cull)) {
-                int l = fi(lo.w), r = fi(hi.w);
-                if (r != l) {  // n == 1 node has left == right (hittable.h:68-72): one visit is enough
-                    stack[sp * stride] = r;
-                    sp++;
-                }
-                ref = l;
-                continue;
+        while (ref >= 0) {  // inner node: test both child boxes
+            const float4 llo = hot4<SM>(sv, (uint32_t)ref), lhi = hot4<SM>(sv, (uint32_t)ref + 16);
+            const float4 rlo = hot4<SM>(sv, (uint32_t)ref + 32), rhi = hot4<SM>(sv, (uint32_t)ref + 48);
+            const float cull = (SHRINK && best_prim >= 0) ? fmaf(best, 4e-6f, best) : tmax;
+            float tl, tr;
+            const bool hl = aabb_hit(llo, lhi, o, inv, tmin, cull, tl);
+            const bool hr = aabb_hit(rlo, rhi, o, inv, tmin, cull, tr);
+            const int l = fi(llo.w), r = fi(lhi.w);
+            if (hl && hr) {
+                const bool left_first = !(tr < tl);
+                stack[sp * stride] = left_first ? r : l;
+                sp++;
+                ref = left_first ? l : r;
+            } else if (hl || hr) {
+                ref = hl ? l : r;
+            } else if (sp > 0) {
+                sp--;
+                ref = stack[sp * stride];
+            } else {
+                ref = kBvhDone;
             }
-        } else {
-            uint2 lf = hot2<SM>(sv, (uint32_t)~ref);
+        }
+        if (ref == kBvhDone) break;
+        {  // leaf: list semantics against the caller's tmax
+            const uint2 lf = hot2<SM>(sv, (uint32_t)~ref);
             float t_leaf = tmax;
             int p_leaf = -1;
             test_groups<F, SM>(sv, lf.x, lf.y, rk, time, tmin, t_leaf, p_leaf);
-            if (p_leaf >= 0 && (best_prim < 0 || t_leaf <= best)) {
+            const int leaf = ~ref;
+            if (p_leaf >= 0 && (best_prim < 0 || t_leaf < best || (t_leaf == best && leaf >= best_leaf))) {
                 best = t_leaf;
                 best_prim = p_leaf;
+                best_leaf = leaf;
+            }
+            if (sp > 0) {
+                sp--;
+                ref = stack[sp * stride];
+            } else {
+                ref = kBvhDone;
             }
         }
-        if (sp == 0) break;
-        sp--;
-        ref = stack[sp * stride];
+        if (ref == kBvhDone) break;
     }
     if (best_prim >= 0) {
         t_out = best;
