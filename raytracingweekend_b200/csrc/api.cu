@@ -371,31 +371,47 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
         nodes[i] = d;
     }
 
-    // (2) trees built here over long hittable_lists (hittable_list.h:11-37 walks them linearly; the closest hit is the
-    // same, the reference's order-dependent tie rules only matter for bit-equal t of different primitives)
+    // (2) trees built here (binned SAH).  Two uses, same builder over "objects" = (box, what the leaf holds):
+    //   * a long hittable_list (hittable_list.h:11-37 walks it linearly): objects are its primitives, leaves hold up to 4;
+    //     the closest hit is the same, the list's order-dependent tie rules only matter for bit-equal t of different prims;
+    //   * the leaves of a reference bvh_node tree, for the RENDER path: the reference topology (random split axis) is kept in
+    //     the flat scene and walked by intersect_batch; rendering walks a SAH tree over the very same leaf objects — one
+    //     reference leaf per tree leaf, same leaf offsets — so the winner, including the right-most-leaf tie rule, is the same.
+    struct Obj {
+        Box box;   // unpadded
+        int id;    // primitive index, or reference leaf index
+    };
     int list_bvh_min = 32;
     if (const char* env = getenv("RTW_LIST_BVH_MIN")) list_bvh_min = atoi(env);
+    bool rebuild_ref = true;
+    if (const char* env = getenv("RTW_RENDER_REF_TOPOLOGY")) rebuild_ref = atoi(env) == 0;
     int max_depth = 0;
-    std::function<int(std::vector<int>&, int)> build_list = [&](std::vector<int>& ids, int depth) -> int {
+    auto node_box = [&](int ref) {
+        if (ref < 0) return leaf_box[~ref];
+        Box b;  // union of the node's two child boxes (already padded and rounded outwards)
+        const DevNode& c = nodes[ref];
+        b.grow_point(c.llo.x, c.llo.y, c.llo.z), b.grow_point(c.lhi.x, c.lhi.y, c.lhi.z);
+        if (c.rlo.x <= c.rhi.x) b.grow_point(c.rlo.x, c.rlo.y, c.rlo.z), b.grow_point(c.rhi.x, c.rhi.y, c.rhi.z);
+        return b;
+    };
+    std::function<int(std::vector<Obj>&, int, bool)> build_tree = [&](std::vector<Obj>& objs, int depth, bool prims) -> int {
         if (depth > max_depth) max_depth = depth;
-        auto make_leaf = [&](std::vector<int>& leaf_ids) {
-            std::sort(leaf_ids.begin(), leaf_ids.end());  // list order inside the leaf
-            int2 lf;
-            add_groups_of(leaf_ids, lf.x, lf.y);
+        auto make_leaf = [&](std::vector<Obj>& lo) {
+            if (!prims) return ~lo[0].id;  // an existing reference leaf
+            std::vector<int> ids;
             Box b;
-            for (int p : leaf_ids) b.merge(prim_box(p));
+            for (auto& o : lo) ids.push_back(o.id), b.merge(o.box);
+            std::sort(ids.begin(), ids.end());  // list order inside the leaf
+            int2 lf;
+            add_groups_of(ids, lf.x, lf.y);
             leaves.push_back(lf);
             leaf_box.push_back(padded(b));
             return ~(int)(leaves.size() - 1);
         };
-        if (ids.size() <= 2) return make_leaf(ids);
+        if (objs.size() == 1 || (prims && objs.size() <= 2)) return make_leaf(objs);
         // binned SAH on centroids (16 bins, 3 axes)
         Box cb;
-        std::vector<Box> pbx(ids.size());
-        for (size_t k = 0; k < ids.size(); k++) {
-            pbx[k] = prim_box(ids[k]);
-            cb.grow_point(pbx[k].centre(0), pbx[k].centre(1), pbx[k].centre(2));
-        }
+        for (auto& o : objs) cb.grow_point(o.box.centre(0), o.box.centre(1), o.box.centre(2));
         double best_cost = 1e300;
         int best_axis = -1, best_bin = 0;
         const int NB = 16;
@@ -404,9 +420,9 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
             if (!(ext > 1e-12)) continue;
             Box bb[NB];
             int cnt[NB] = {};
-            for (size_t k = 0; k < ids.size(); k++) {
-                int bi = std::min(NB - 1, (int)((pbx[k].centre(ax) - lo) / ext * NB));
-                bb[bi].merge(pbx[k]);
+            for (auto& o : objs) {
+                int bi = std::min(NB - 1, (int)((o.box.centre(ax) - lo) / ext * NB));
+                bb[bi].merge(o.box);
                 cnt[bi]++;
             }
             Box lb[NB], rb[NB];
@@ -422,49 +438,55 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
                 if (cost < best_cost) best_cost = cost, best_axis = ax, best_bin = k;
             }
         }
-        std::vector<int> L, R;
+        std::vector<Obj> L, R;
         if (best_axis >= 0) {
             double lo = cb.lo[best_axis], ext = cb.hi[best_axis] - cb.lo[best_axis];
-            for (size_t k = 0; k < ids.size(); k++) {
-                int bi = std::min(NB - 1, (int)((pbx[k].centre(best_axis) - lo) / ext * NB));
-                (bi <= best_bin ? L : R).push_back(ids[k]);
+            for (auto& o : objs) {
+                int bi = std::min(NB - 1, (int)((o.box.centre(best_axis) - lo) / ext * NB));
+                (bi <= best_bin ? L : R).push_back(o);
             }
         }
-        if (L.empty() || R.empty()) {  // coincident centroids: split in list order
-            L.assign(ids.begin(), ids.begin() + ids.size() / 2);
-            R.assign(ids.begin() + ids.size() / 2, ids.end());
+        if (L.empty() || R.empty()) {  // coincident centroids: split in order
+            L.assign(objs.begin(), objs.begin() + objs.size() / 2);
+            R.assign(objs.begin() + objs.size() / 2, objs.end());
         }
         // leaves of up to 4 primitives when splitting further does not pay (SAH with node cost ~ 2 primitive tests)
-        if (ids.size() <= 4) {
-            Box all;
-            for (auto& b : pbx) all.merge(b);
-            Box lbx, rbx;
-            for (int p : L) lbx.merge(prim_box(p));
-            for (int p : R) rbx.merge(prim_box(p));
+        if (prims && objs.size() <= 4) {
+            Box all, lbx, rbx;
+            for (auto& o : objs) all.merge(o.box);
+            for (auto& o : L) lbx.merge(o.box);
+            for (auto& o : R) rbx.merge(o.box);
             double split_cost = 2.0 + (lbx.area() * L.size() + rbx.area() * R.size()) / std::max(all.area(), 1e-300);
-            if (split_cost >= (double)ids.size()) return make_leaf(ids);
+            if (split_cost >= (double)objs.size()) return make_leaf(objs);
         }
         int idx = (int)nodes.size();
         nodes.push_back(DevNode{});
-        int lref = build_list(L, depth + 1), rref = build_list(R, depth + 1);
+        int lref = build_tree(L, depth + 1, prims), rref = build_tree(R, depth + 1, prims);
         DevNode d{};
-        auto child_box = [&](int ref) {
-            if (ref < 0) return leaf_box[~ref];
-            Box b;  // union of the child's two child boxes (already padded and rounded outwards)
-            const DevNode& c = nodes[ref];
-            b.grow_point(c.llo.x, c.llo.y, c.llo.z), b.grow_point(c.lhi.x, c.lhi.y, c.lhi.z);
-            if (c.rlo.x <= c.rhi.x) b.grow_point(c.rlo.x, c.rlo.y, c.rlo.z), b.grow_point(c.rhi.x, c.rhi.y, c.rhi.z);
-            return b;
-        };
-        Box lb = child_box(lref), rb = child_box(rref);
+        Box lb = node_box(lref), rb = node_box(rref);
         set_child(d, false, &lb, lref);
         set_child(d, true, &rb, rref);
         nodes[idx] = d;
         return idx;
     };
+    auto pseudo_root = [&](int root) {  // left child = the tree, right child empty
+        DevNode pr{};
+        Box rb = node_box(root);
+        set_child(pr, false, &rb, root);
+        set_child(pr, true, nullptr, root);
+        nodes.push_back(pr);
+        return (int)nodes.size() - 1;
+    };
+    std::function<void(int, std::vector<int>&)> collect_leaves = [&](int ref, std::vector<int>& out) {
+        if (ref < 0) {
+            out.push_back(~ref);
+            return;
+        }
+        collect_leaves(fs->nodes[ref].left, out);
+        if (fs->nodes[ref].right != fs->nodes[ref].left) collect_leaves(fs->nodes[ref].right, out);
+    };
 
     std::vector<DevItem> items(fs->n_items);
-    std::vector<std::pair<int, Box>> roots;  // (item, root box) of every tree: pseudo-roots are appended below
     for (int i = 0; i < fs->n_items; i++) {
         const rtw_flat_item& it = fs->items[i];
         DevItem d{};
@@ -475,31 +497,32 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
             feat |= F_BVH;
             int dep = bvh_depth(fs, it.first, 0);
             if (dep > max_depth) max_depth = dep;
-            DevNode pr{};
+            DevNode pr{};  // exact path: the reference's own root box
             exact_child(pr, false, fs->nodes[it.first].bmin, fs->nodes[it.first].bmax, it.first);
             set_child(pr, true, nullptr, it.first);
             d.first = (int)nodes.size();
             nodes.push_back(pr);
+            d.end = d.first;
+            if (rebuild_ref) {
+                std::vector<int> lv;
+                collect_leaves(it.first, lv);
+                std::sort(lv.begin(), lv.end());
+                lv.erase(std::unique(lv.begin(), lv.end()), lv.end());
+                std::vector<Obj> objs;
+                for (int l : lv) {
+                    Obj o;
+                    o.id = l;
+                    for (int p = 0; p < fs->leaves[l].prim_count; p++) o.box.merge(prim_box(fs->leaves[l].first_prim + p));
+                    objs.push_back(o);
+                }
+                d.end = pseudo_root(build_tree(objs, 1, false));
+            }
         } else if (it.type == RTW_ITEM_PRIMS && list_bvh_min > 0 && it.count >= list_bvh_min) {
             feat |= F_BVH;
-            std::vector<int> ids(it.count);
-            for (int k = 0; k < it.count; k++) ids[k] = it.first + k;
-            int root = build_list(ids, 1);
-            DevNode pr{};
-            Box rb;
-            if (root >= 0) {
-                const DevNode& c = nodes[root];
-                rb.grow_point(c.llo.x, c.llo.y, c.llo.z), rb.grow_point(c.lhi.x, c.lhi.y, c.lhi.z);
-                if (c.rlo.x <= c.rhi.x) rb.grow_point(c.rlo.x, c.rlo.y, c.rlo.z), rb.grow_point(c.rhi.x, c.rhi.y, c.rhi.z);
-            } else {
-                rb = leaf_box[~root];
-            }
-            set_child(pr, false, &rb, root);
-            set_child(pr, true, nullptr, root);
+            std::vector<Obj> objs(it.count);
+            for (int k = 0; k < it.count; k++) objs[k].id = it.first + k, objs[k].box = prim_box(it.first + k);
             d.type = RTW_ITEM_BVH;
-            d.first = (int)nodes.size();
-            d.end = 0;
-            nodes.push_back(pr);
+            d.first = d.end = pseudo_root(build_tree(objs, 1, true));
         } else {
             add_groups(it.first, it.count, d.first, d.end);
         }
@@ -596,7 +619,7 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
     }
     for (DevItem& d : items) {
         d.xf = xf_off(d.xf);
-        if (d.type == RTW_ITEM_BVH) d.first = ref_off(d.first), d.end = 0;
+        if (d.type == RTW_ITEM_BVH) d.first = ref_off(d.first), d.end = ref_off(d.end);
         else d.first = group_off(d.first), d.end = group_off(d.end);
     }
     for (DevNode& n : nodes) {

@@ -294,6 +294,18 @@ RTW_DEV bool aabb_hit(float4 lo, float4 hi, V3 o, V3 inv, float tmin, float tmax
     return ok;
 }
 
+// Conservative slab test for the trees this backend builds itself (padded boxes, rounded outwards): min/max form, the
+// reference's NaN conventions are not needed — fminf/fmaxf drop a NaN slab (0 * inf), which only widens the interval.
+RTW_DEV bool slab_hit(float4 lo, float4 hi, V3 inv, V3 oi, float tmin, float tmax, float& t_entry) {
+    const float x0 = fmaf(lo.x, inv.x, -oi.x), x1 = fmaf(hi.x, inv.x, -oi.x);
+    const float y0 = fmaf(lo.y, inv.y, -oi.y), y1 = fmaf(hi.y, inv.y, -oi.y);
+    const float z0 = fmaf(lo.z, inv.z, -oi.z), z1 = fmaf(hi.z, inv.z, -oi.z);
+    const float tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), tmin));
+    const float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), tmax));
+    t_entry = tn;
+    return tn <= tf;
+}
+
 // ------------------------------------------------------------------------------------------------ closest hit
 // Result of world.hit(): winning primitive (or medium item) and t.  Normal/uv/p are reconstructed afterwards
 // from the id (complete_hit), so the search loop carries two registers.
