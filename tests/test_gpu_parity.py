@@ -252,3 +252,34 @@ def test_wavefront_ragged_shapes_shards_and_accumulate(scenes):
     assert np.all(out[..., 3] == 16) and np.allclose(out[..., :3], full[..., :3], rtol=1e-4, atol=1e-4)
     with pytest.raises(rtw._lib.RtwError):
         sc.render(8, 8, 1, max_depth=300, flags=WF)
+
+
+def test_upload_time_trees_do_not_change_hits_or_images():
+    """The trees built at upload (SAH over a long hittable_list; SAH over the leaves of a reference bvh_node tree for the
+    render path) are accelerations only: with them switched off (RTW_LIST_BVH_MIN=0, RTW_RENDER_REF_TOPOLOGY=1 — read at
+    rtw_scene_create) the same rays hit the same primitives at the same t, and renders with the same Philox keys agree."""
+    g = np.load(os.path.join(GOLDEN, "hits_random_balls_scene.npz"))
+    rays = g["rays"].astype(np.float32)
+    b = builder_for("random_balls_scene", float(g["aspect"]))
+    fast = rtw.Scene(b)
+    os.environ["RTW_LIST_BVH_MIN"] = "0"
+    try:
+        plain = rtw.Scene(b)
+    finally:
+        del os.environ["RTW_LIST_BVH_MIN"]
+    hf, hp = fast.intersect_batch(rays), plain.intersect_batch(rays)
+    assert np.array_equal(hf["prim"], hp["prim"]) and np.array_equal(hf["t"], hp["t"])
+    a, sa = fast.render(48, 32, 4, seed=3)
+    c, sc_ = plain.render(48, 32, 4, seed=3)
+    assert sa["rays"] == sc_["rays"] and np.array_equal(a, c)
+
+    b2 = builder_for("book2_final_scene", 1.0)
+    sah = rtw.Scene(b2)
+    os.environ["RTW_RENDER_REF_TOPOLOGY"] = "1"
+    try:
+        ref = rtw.Scene(b2)
+    finally:
+        del os.environ["RTW_RENDER_REF_TOPOLOGY"]
+    a, sa = sah.render(32, 32, 4, seed=3)
+    c, sc_ = ref.render(32, 32, 4, seed=3)
+    assert sa["rays"] == sc_["rays"] and np.array_equal(a, c)
