@@ -345,60 +345,89 @@ RTW_DEV RayK xf_rayk(const DevXf& x, const RayK& w) {
 // (:26-34) re-selects the same winner for deterministic children.
 // All loop bounds and record addresses are warp-uniform: one broadcast load per 16 bytes.  Loops are kept rolled
 // (`unroll 1`): trip counts are tiny (Cornell: 1-3) and unrolled remainders cost more branches than they save.
+// Loads at an ABSOLUTE address: for staged sections the 32-bit shared address (sbase already added, so the inner loops
+// advance one register and every LDS is [reg + imm]); for unstaged ones the blob offset.
+template <int SM>
+RTW_DEV uint32_t hot_abs(const SceneView& sv, uint32_t off) { return (SM >= 1) ? sv.sbase + off : off; }
+template <int SM>
+RTW_DEV float4 hot4_abs(const SceneView& sv, uint32_t addr) {
+    float4 v;
+    if constexpr (SM >= 1) {
+        asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    } else {
+        v = __ldg(reinterpret_cast<const float4*>(sv.g + addr));
+    }
+    return v;
+}
+
+// The five kind loops of one group, for ray constants `k` already in the group's frame.
+template <uint32_t F, int SM>
+RTW_DEV void test_group_kinds(const SceneView& sv, float4 g0, float4 g1, const RayK& k, float time, float tmin, float& t_best,
+                              int& prim_best) {
+    const uint32_t sph0 = hot_abs<SM>(sv, (uint32_t)fi(g0.y)), sph1 = hot_abs<SM>(sv, (uint32_t)fi(g0.z));
+    const uint32_t msph1 = hot_abs<SM>(sv, (uint32_t)fi(g0.w));
+    const uint32_t xy1 = hot_abs<SM>(sv, (uint32_t)fi(g1.x)), xz1 = hot_abs<SM>(sv, (uint32_t)fi(g1.y));
+    const uint32_t yz1 = hot_abs<SM>(sv, (uint32_t)fi(g1.z));
+#pragma unroll 1
+    for (uint32_t r = sph0; r < sph1; r += 32) {
+        float4 ra = hot4_abs<SM>(sv, r), rb = hot4_abs<SM>(sv, r + 16);
+        int id = fi(rb.w);
+        float t0, t1, t;
+        bool roots;
+        if ((F & F_PRECISE) && (id & REC_PRECISE)) {
+            roots = sphere_roots_f64<SM>(sv, (uint32_t)fi(rb.x), k.o, k.d, t0, t1);
+            id &= ~REC_PRECISE;
+        } else {
+            roots = sphere_roots(k.o - mk(ra.x, ra.y, ra.z), k.d, k.a, k.inv_a, ra.w, t0, t1);
+        }
+        if (roots && sphere_pick(t0, t1, tmin, t_best, t)) {
+            t_best = t;
+            prim_best = id;
+        }
+    }
+    if (F & F_MOVING) {
+#pragma unroll 1
+        for (uint32_t r = sph1; r < msph1; r += 32) {
+            float4 ra = hot4_abs<SM>(sv, r), rb = hot4_abs<SM>(sv, r + 16);
+            // sphere.h:22-25 folded to c' + time*delta on the host
+            V3 c = madd(mk(ra.x, ra.y, ra.z), time, mk(rb.x, rb.y, rb.z));
+            float t0, t1, t;
+            if (sphere_roots(k.o - c, k.d, k.a, k.inv_a, ra.w, t0, t1) && sphere_pick(t0, t1, tmin, t_best, t)) {
+                t_best = t;
+                prim_best = fi(rb.w);
+            }
+        }
+    }
+#pragma unroll 1
+    for (uint32_t r = msph1; r < xy1; r += 32) {  // xy_rect: plane z = k
+        float4 ra = hot4_abs<SM>(sv, r), rb = hot4_abs<SM>(sv, r + 16);
+        rect_update(ra, rb.x, fi(rb.w), k.o.z, k.inv.z, k.o.x, k.d.x, k.o.y, k.d.y, tmin, t_best, prim_best);
+    }
+#pragma unroll 1
+    for (uint32_t r = xy1; r < xz1; r += 32) {  // xz_rect: plane y = k
+        float4 ra = hot4_abs<SM>(sv, r), rb = hot4_abs<SM>(sv, r + 16);
+        rect_update(ra, rb.x, fi(rb.w), k.o.y, k.inv.y, k.o.x, k.d.x, k.o.z, k.d.z, tmin, t_best, prim_best);
+    }
+#pragma unroll 1
+    for (uint32_t r = xz1; r < yz1; r += 32) {  // yz_rect: plane x = k
+        float4 ra = hot4_abs<SM>(sv, r), rb = hot4_abs<SM>(sv, r + 16);
+        rect_update(ra, rb.x, fi(rb.w), k.o.x, k.inv.x, k.o.y, k.d.y, k.o.z, k.d.z, tmin, t_best, prim_best);
+    }
+}
+
 template <uint32_t F, int SM>
 RTW_DEV void test_groups(const SceneView& sv, uint32_t gfirst, uint32_t gend, const RayK& rk, float time, float tmin,
                          float& t_best, int& prim_best) {
+    const uint32_t ga0 = hot_abs<SM>(sv, gfirst), ga1 = hot_abs<SM>(sv, gend);
 #pragma unroll 1
-    for (uint32_t ga = gfirst; ga < gend; ga += 32) {
-        float4 g0 = hot4<SM>(sv, ga), g1 = hot4<SM>(sv, ga + 16);
-        RayK k = rk;
-        if ((F & F_XF) && fi(g0.x) >= 0) k = xf_rayk(ld_xf<SM>(sv, (uint32_t)fi(g0.x)), rk);
-        const uint32_t sph0 = (uint32_t)fi(g0.y), sph1 = (uint32_t)fi(g0.z), msph1 = (uint32_t)fi(g0.w);
-        const uint32_t xy1 = (uint32_t)fi(g1.x), xz1 = (uint32_t)fi(g1.y), yz1 = (uint32_t)fi(g1.z);
-#pragma unroll 1
-        for (uint32_t r = sph0; r < sph1; r += 32) {
-            float4 ra = hot4<SM>(sv, r), rb = hot4<SM>(sv, r + 16);
-            int id = fi(rb.w);
-            float t0, t1, t;
-            bool roots;
-            if ((F & F_PRECISE) && (id & REC_PRECISE)) {
-                roots = sphere_roots_f64<SM>(sv, (uint32_t)fi(rb.x), k.o, k.d, t0, t1);
-                id &= ~REC_PRECISE;
-            } else {
-                roots = sphere_roots(k.o - mk(ra.x, ra.y, ra.z), k.d, k.a, k.inv_a, ra.w, t0, t1);
-            }
-            if (roots && sphere_pick(t0, t1, tmin, t_best, t)) {
-                t_best = t;
-                prim_best = id;
-            }
-        }
-        if (F & F_MOVING) {
-#pragma unroll 1
-            for (uint32_t r = sph1; r < msph1; r += 32) {
-                float4 ra = hot4<SM>(sv, r), rb = hot4<SM>(sv, r + 16);
-                // sphere.h:22-25 folded to c' + time*delta on the host
-                V3 c = madd(mk(ra.x, ra.y, ra.z), time, mk(rb.x, rb.y, rb.z));
-                float t0, t1, t;
-                if (sphere_roots(k.o - c, k.d, k.a, k.inv_a, ra.w, t0, t1) && sphere_pick(t0, t1, tmin, t_best, t)) {
-                    t_best = t;
-                    prim_best = fi(rb.w);
-                }
-            }
-        }
-#pragma unroll 1
-        for (uint32_t r = msph1; r < xy1; r += 32) {  // xy_rect: plane z = k
-            float4 ra = hot4<SM>(sv, r), rb = hot4<SM>(sv, r + 16);
-            rect_update(ra, rb.x, fi(rb.w), k.o.z, k.inv.z, k.o.x, k.d.x, k.o.y, k.d.y, tmin, t_best, prim_best);
-        }
-#pragma unroll 1
-        for (uint32_t r = xy1; r < xz1; r += 32) {  // xz_rect: plane y = k
-            float4 ra = hot4<SM>(sv, r), rb = hot4<SM>(sv, r + 16);
-            rect_update(ra, rb.x, fi(rb.w), k.o.y, k.inv.y, k.o.x, k.d.x, k.o.z, k.d.z, tmin, t_best, prim_best);
-        }
-#pragma unroll 1
-        for (uint32_t r = xz1; r < yz1; r += 32) {  // yz_rect: plane x = k
-            float4 ra = hot4<SM>(sv, r), rb = hot4<SM>(sv, r + 16);
-            rect_update(ra, rb.x, fi(rb.w), k.o.x, k.inv.x, k.o.y, k.d.y, k.o.z, k.d.z, tmin, t_best, prim_best);
+    for (uint32_t ga = ga0; ga < ga1; ga += 32) {
+        const float4 g0 = hot4_abs<SM>(sv, ga), g1 = hot4_abs<SM>(sv, ga + 16);
+        // two instantiations of the kind loops instead of `k = xf ? xf_rayk(rk) : rk`: no 11-register copy per group
+        if ((F & F_XF) && fi(g0.x) >= 0) {
+            const RayK k = xf_rayk(ld_xf<SM>(sv, (uint32_t)fi(g0.x)), rk);
+            test_group_kinds<F, SM>(sv, g0, g1, k, time, tmin, t_best, prim_best);
+        } else {
+            test_group_kinds<F, SM>(sv, g0, g1, rk, time, tmin, t_best, prim_best);
         }
     }
 }
