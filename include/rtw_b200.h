@@ -318,6 +318,15 @@ int rtw_tonemap(const float* accum_rgba, int nx, int ny, double* canvas_rgb);
 /* RayTracingWeekend.cpp:252-275: "P3", top row first, int(255.99f*c), one pixel per line. */
 int rtw_write_ppm(const char* path, const double* canvas_rgb, int nx, int ny);
 
+/* "P6" binary twin of rtw_write_ppm: same rows, same int(255.99f*c) quantisation (RayTracingWeekend.cpp:252-275). */
+int rtw_write_ppm_binary(const char* path, const double* canvas_rgb, int nx, int ny);
+/* 8-bit RGB PNG of the same pixels — replaces `system("magick 1.ppm 1.png")` (RayTracingWeekend.cpp:285). */
+int rtw_write_png(const char* path, const double* canvas_rgb, int nx, int ny);
+/* Texture ingest for image_texture (texture.h:73-99 takes caller-decoded bytes; the reference ships earth.jpg but no
+ * loader): baseline JPEG -> RGB8 rows, top row first.  rgb8 == NULL only reports the size.  RTW_ERR_UNSUPPORTED for
+ * progressive / arithmetic / >2x subsampled files. */
+int rtw_decode_jpeg(const uint8_t* data, size_t size, uint8_t* rgb8, size_t rgb8_capacity, int* out_nx, int* out_ny);
+
 /* Measured FP32 FFMA throughput of `device` in TFLOP/s (roofline denominator). */
 int rtw_measure_fp32_peak(int device, double* tflops);
 /* Device utility: number of CUDA devices with compute capability 10.x (0 = none / no driver). */

@@ -134,6 +134,9 @@ SIGNATURES = {
     "rtw_intersect_batch_device": (C.c_int, [_P, _P, _P, C.c_int64, C.c_float, C.c_float, _P]),
     "rtw_tonemap": (C.c_int, [_P, C.c_int, C.c_int, _P]),
     "rtw_write_ppm": (C.c_int, [C.c_char_p, _P, C.c_int, C.c_int]),
+    "rtw_write_ppm_binary": (C.c_int, [C.c_char_p, _P, C.c_int, C.c_int]),
+    "rtw_write_png": (C.c_int, [C.c_char_p, _P, C.c_int, C.c_int]),
+    "rtw_decode_jpeg": (C.c_int, [_P, C.c_size_t, _P, C.c_size_t, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "rtw_device_count": (C.c_int, []),
     "rtw_measure_fp32_peak": (C.c_int, [C.c_int, C.POINTER(C.c_double)]),
 }

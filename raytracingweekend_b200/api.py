@@ -222,6 +222,33 @@ def tonemap(accum: np.ndarray) -> np.ndarray:
     return out
 
 
+def write_ppm_binary(path: str, canvas: np.ndarray) -> None:
+    """"P6" twin of write_ppm (same rows, same quantisation) via rtw_write_ppm_binary."""
+    l = _lib.load()
+    ny, nx = canvas.shape[:2]
+    c = np.ascontiguousarray(canvas, dtype=np.float64)
+    check(l.rtw_write_ppm_binary(path.encode(), c.ctypes.data_as(C.c_void_p), nx, ny), "rtw_write_ppm_binary")
+
+
+def write_png(path: str, canvas: np.ndarray) -> None:
+    """8-bit RGB PNG of the canvas (replaces the reference's `magick 1.ppm 1.png`, RayTracingWeekend.cpp:285)."""
+    l = _lib.load()
+    ny, nx = canvas.shape[:2]
+    c = np.ascontiguousarray(canvas, dtype=np.float64)
+    check(l.rtw_write_png(path.encode(), c.ctypes.data_as(C.c_void_p), nx, ny), "rtw_write_png")
+
+
+def decode_jpeg(data: bytes) -> np.ndarray:
+    """Baseline JPEG -> [ny, nx, 3] uint8, top row first: the byte array image_texture takes (texture.h:73-99)."""
+    l = _lib.load()
+    buf = (C.c_uint8 * len(data)).from_buffer_copy(data)
+    nx, ny = C.c_int(), C.c_int()
+    check(l.rtw_decode_jpeg(buf, len(data), None, 0, C.byref(nx), C.byref(ny)), "rtw_decode_jpeg")
+    out = np.empty((ny.value, nx.value, 3), dtype=np.uint8)
+    check(l.rtw_decode_jpeg(buf, len(data), out.ctypes.data_as(C.c_void_p), out.size, C.byref(nx), C.byref(ny)), "rtw_decode_jpeg")
+    return out
+
+
 def write_ppm(path: str, canvas: np.ndarray) -> None:
     """RayTracingWeekend.cpp:252-275 via rtw_write_ppm."""
     l = _lib.load()

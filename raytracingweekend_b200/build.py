@@ -17,7 +17,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "lib")
 OBJ = os.path.join(HERE, "build")
 
-HOST_SRCS = ["builder.cpp", "scenes.cpp", "hostio.cpp"]
+HOST_SRCS = ["builder.cpp", "scenes.cpp", "hostio.cpp", "imageio.cpp"]
 CUDA_SRCS = ["kernels.cu", "wavefront.cu", "api.cu"]
 NVCC_ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 CXXFLAGS = ["-std=c++17", "-O2", "-fPIC", "-Wall"]
