@@ -266,7 +266,11 @@ void rtw_scene_destroy(rtw_scene* s);
 enum { /* rtw_render_params.flags */
     RTW_FLAG_WAVEFRONT = 1u << 0,   /* use the wavefront pipeline instead of the megakernel      */
     RTW_FLAG_ACCUMULATE = 1u << 1,  /* add into accum instead of overwriting (progressive/resume) */
-    RTW_FLAG_DEBUG_RAY = 1u << 2    /* RayTracingWeekend.cpp:221-225: aim every sample at the centre pixel */
+    RTW_FLAG_DEBUG_RAY = 1u << 2,   /* RayTracingWeekend.cpp:221-225: aim every sample at the centre pixel */
+    RTW_FLAG_AUTO = 1u << 3         /* let the backend pick megakernel or wavefront from the scene's features: the wavefront
+                                       pipeline where shading is heavy and divergent (Perlin noise textures; bvh_node trees
+                                       together with media) — the ncu evidence is in profiles/ — the megakernel otherwise.  Sums are then only
+                                       reproducible up to the order of float adds. */
 };
 
 typedef struct rtw_render_params {

@@ -118,3 +118,52 @@ public:
         this->background_type = BackgroundType::Black;
     }
 };
+
+// Book 2 "Cornell smoke" (Volume.png): both boxes as constant_medium boundaries.  Twin of scenes.cpp cornell_smoke_scene.
+class cornell_smoke_scene : public scene {
+public:
+    cornell_smoke_scene(double aspect) : scene() {
+        std::shared_ptr<texture> red_tex = std::make_shared<constant_texture>(vec3(0.65f, 0.05f, 0.05f));
+        auto red = std::make_shared<lambertian>(red_tex);
+        std::shared_ptr<texture> white_tex = std::make_shared<constant_texture>(vec3(0.73f, 0.73f, 0.73f));
+        auto white = std::make_shared<lambertian>(white_tex);
+        std::shared_ptr<texture> green_tex = std::make_shared<constant_texture>(vec3(0.12f, 0.45f, 0.15f));
+        auto green = std::make_shared<lambertian>(green_tex);
+        std::shared_ptr<texture> light_tex = std::make_shared<constant_texture>(vec3(7.0, 7.0, 7.0));
+        auto light = std::make_shared<diffuse_light>(light_tex);
+        std::vector<std::shared_ptr<hittable>> objects;
+        objects.push_back(std::make_shared<xz_rect>(113.0, 443.0, 127.0, 432.0, 554.0, light));
+        lights->objects.push_back(objects.back());
+        objects.push_back(std::make_shared<flip_normals>(std::make_shared<yz_rect>(0.0, 555.0, 0.0, 555.0, 555.0, green)));
+        objects.push_back(std::make_shared<yz_rect>(0.0, 555.0, 0.0, 555.0, 0.0, red));
+        objects.push_back(std::make_shared<flip_normals>(std::make_shared<xz_rect>(0.0, 555.0, 0.0, 555.0, 555.0, white)));
+        objects.push_back(std::make_shared<xz_rect>(0.0, 555.0, 0.0, 555.0, 0.0, white));
+        objects.push_back(std::make_shared<flip_normals>(std::make_shared<xy_rect>(0.0, 555.0, 0.0, 555.0, 555.0, white)));
+        std::shared_ptr<hittable> b1 = std::make_shared<translate>(
+            std::make_shared<rotate_y>(std::make_shared<box>(vec3(0.0, 0.0, 0.0), vec3(165.0, 165.0, 165.0), white), -18.0),
+            vec3(130.0, 0.0, 65.0));
+        std::shared_ptr<hittable> b2 = std::make_shared<translate>(
+            std::make_shared<rotate_y>(std::make_shared<box>(vec3(0.0, 0.0, 0.0), vec3(165.0, 330.0, 165.0), white), 15.0),
+            vec3(265.0, 0.0, 295.0));
+        std::shared_ptr<texture> smoke_white = std::make_shared<constant_texture>(vec3(1.0, 1.0, 1.0));
+        std::shared_ptr<texture> smoke_black = std::make_shared<constant_texture>(vec3(0.0, 0.0, 0.0));
+        objects.push_back(std::make_shared<constant_medium>(b1, 0.01, std::make_shared<isotropic>(smoke_white)));
+        objects.push_back(std::make_shared<constant_medium>(b2, 0.01, std::make_shared<isotropic>(smoke_black)));
+        this->world = hittable_list(objects);
+        this->cam = camera(vec3(278.0, 278.0, -800.0), vec3(278.0, 278.0, 0.0), vec3(0.0, 1.0, 0.0), 40.0, aspect, 0.0, 10.0, 0.0, 1.0);
+        this->background_type = BackgroundType::Black;
+    }
+};
+
+// Book 2 "two checker spheres".  Twin of scenes.cpp checker_spheres_scene.
+class checker_spheres_scene : public scene {
+public:
+    checker_spheres_scene(double aspect) : scene() {
+        std::shared_ptr<texture> even = std::make_shared<constant_texture>(vec3(0.2, 0.3, 0.1));
+        std::shared_ptr<texture> odd = std::make_shared<constant_texture>(vec3(0.9, 0.9, 0.9));
+        std::shared_ptr<texture> checker = std::make_shared<checker_texture>(even, odd);
+        Add(std::make_shared<sphere>(vec3(0, -10, 0), 10.0, std::make_shared<lambertian>(checker)));
+        Add(std::make_shared<sphere>(vec3(0, 10, 0), 10.0, std::make_shared<lambertian>(checker)));
+        this->cam = camera(vec3(13, 2, 3), vec3(0, 0, 0), vec3(0.0, 1.0, 0.0), 20.0, aspect, 0.0, 10.0, 0.0, 1.0);
+    }
+};

@@ -11,6 +11,7 @@ LIB_PATH = os.environ.get("RTW_B200_LIB") or os.path.join(HERE, "lib", "librtw_b
 
 RTW_OK = 0
 RTW_FLAG_WAVEFRONT = 1
+RTW_FLAG_AUTO = 8
 RTW_FLAG_ACCUMULATE = 2
 RTW_FLAG_DEBUG_RAY = 4
 

@@ -19,7 +19,7 @@ from ._lib import RenderParams, RenderStats, check
 GOLDEN_EARTH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests", "golden", "earth_256x256_rgb8.bin")
 
 SCENE_NAMES = ("light_sample", "dielectric_scene", "random_balls_scene", "cornell_box_scene", "cornell_box_aluminum",
-               "two_perlin_spheres_earth", "book2_final_scene")
+               "two_perlin_spheres_earth", "book2_final_scene", "cornell_smoke_scene", "checker_spheres_scene")
 
 
 def _d3(v: Sequence[float]):

@@ -117,6 +117,7 @@ struct rtw_scene {
     int pending_launches = 0;
     float* scratch_accum = nullptr;  // device buffer behind rtw_render (host API)
     size_t scratch_pixels = 0;
+    bool prefer_wavefront = false;  // RTW_FLAG_AUTO: set at upload from what the scene's shading costs
     void* wf_scratch = nullptr;  // wavefront path pool + queues (lazy)
     uint32_t wf_slots = 0;
     unsigned long long* wf_host_flag = nullptr;  // pinned
@@ -666,6 +667,9 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
     d.n_world_items = fs->n_world_items, d.n_items = fs->n_items, d.n_prims = fs->n_prims, d.n_lights = fs->n_lights;
     d.render_type = fs->render_type, d.background_type = fs->background_type;
     d.features = feat, d.max_bvh_depth = max_depth;
+    for (int i = 0; i < fs->n_textures; i++)
+        if (fs->textures[i].type == RTW_TEX_NOISE) s->prefer_wavefront = true;
+    if ((feat & F_MEDIA) && fs->n_nodes > 0) s->prefer_wavefront = true;
     const rtw_flat_camera& c = fs->camera;
     DevCamera& k = d.cam;
     k.ox = (float)c.origin[0], k.oy = (float)c.origin[1], k.oz = (float)c.origin[2];
@@ -720,7 +724,14 @@ extern "C" int rtw_render_device(rtw_scene* s, const rtw_render_params* p, float
     if ((e = cudaMemsetAsync(s->d_counter, 0, sizeof(unsigned long long), st)) != cudaSuccess) return cuda_fail(e, "memset");
     if ((e = cudaEventRecord(s->ev0, st)) != cudaSuccess) return cuda_fail(e, "event");
     int launches = 1;
-    if (p->flags & RTW_FLAG_WAVEFRONT) {
+    bool wavefront = (p->flags & RTW_FLAG_WAVEFRONT) != 0;
+    if ((p->flags & RTW_FLAG_AUTO) && !wavefront) {
+        // measured on B200 (profiles/README.md): the sorted shade kernel pays off when part of each warp would evaluate
+        // 7-octave Perlin turbulence, or walk big trees and media together; Cornell-class scenes (constant or checker
+        // textures, smoke in small boxes, long sphere lists) run faster in the megakernel
+        wavefront = s->prefer_wavefront && p->max_depth <= 255 && (long long)p->spp_begin + p->spp_count < (1 << 24);
+    }
+    if (wavefront) {
         // pool of path slots: L2-resident by default (1 Mi slots = 64 MiB), never larger than the work
         if (p->max_depth > 255 || (long long)p->spp_begin + p->spp_count >= (1 << 24)) {
             set_error("render: the wavefront pipeline packs (sample, bounce) into 24+8 bits: max_depth <= 255, samples < 2^24");

@@ -209,6 +209,39 @@ bool book2_final_scene(rtw_builder* b, double aspect, const uint8_t* earth, int 
     return s.finish({478, 278, -600}, {278, 278, 0}, 40.0, aspect, 0.0, 10.0, RTW_BG_BLACK);
 }
 
+// Book 2 "Cornell smoke" (the reference's Volume.png, README figure): the two boxes become constant_medium boundaries
+// (hittable.h:420-489) — white and black smoke.  Composed from the reference's constructors; the light is the wider,
+// dimmer panel of the book.  Exercises constant_medium over translate(rotate_y(box)) boundaries.
+bool cornell_smoke_scene(rtw_builder* b, double aspect) {
+    SceneCtx s{b};
+    rtw_id red = lambert_const(b, 0.65f, 0.05f, 0.05f);
+    rtw_id white = lambert_const(b, 0.73f, 0.73f, 0.73f);
+    rtw_id green = lambert_const(b, 0.12f, 0.45f, 0.15f);
+    rtw_id light = rtw_diffuse_light(b, rtw_constant_texture(b, 7.0, 7.0, 7.0));
+    s.add(rtw_xz_rect(b, 113.0, 443.0, 127.0, 432.0, 554.0, light));
+    s.lights.push_back(s.objects.back());
+    s.add(rtw_flip_normals(b, rtw_yz_rect(b, 0.0, 555.0, 0.0, 555.0, 555.0, green)));
+    s.add(rtw_yz_rect(b, 0.0, 555.0, 0.0, 555.0, 0.0, red));
+    s.add(rtw_flip_normals(b, rtw_xz_rect(b, 0.0, 555.0, 0.0, 555.0, 555.0, white)));
+    s.add(rtw_xz_rect(b, 0.0, 555.0, 0.0, 555.0, 0.0, white));
+    s.add(rtw_flip_normals(b, rtw_xy_rect(b, 0.0, 555.0, 0.0, 555.0, 555.0, white)));
+    double p0[3] = {0.0, 0.0, 0.0}, p1[3] = {165.0, 165.0, 165.0}, p2[3] = {165.0, 330.0, 165.0};
+    rtw_id b1 = rtw_translate(b, rtw_rotate_y(b, rtw_box(b, p0, p1, white), -18.0), 130.0, 0.0, 65.0);
+    rtw_id b2 = rtw_translate(b, rtw_rotate_y(b, rtw_box(b, p0, p2, white), 15.0), 265.0, 0.0, 295.0);
+    s.add(rtw_constant_medium(b, b1, 0.01, rtw_isotropic(b, rtw_constant_texture(b, 1.0, 1.0, 1.0))));
+    s.add(rtw_constant_medium(b, b2, 0.01, rtw_isotropic(b, rtw_constant_texture(b, 0.0, 0.0, 0.0))));
+    return s.finish({278.0, 278.0, -800.0}, {278.0, 278.0, 0.0}, 40.0, aspect, 0.0, 10.0, RTW_BG_BLACK);
+}
+
+// Book 2 "two checker spheres": checker_texture (texture.h:29-50) on two large spheres under the gradient sky.
+bool checker_spheres_scene(rtw_builder* b, double aspect) {
+    SceneCtx s{b};
+    rtw_id checker = rtw_checker_texture(b, rtw_constant_texture(b, 0.2, 0.3, 0.1), rtw_constant_texture(b, 0.9, 0.9, 0.9));
+    s.add(rtw_sphere(b, 0, -10, 0, 10.0, rtw_lambertian(b, checker)));
+    s.add(rtw_sphere(b, 0, 10, 0, 10.0, rtw_lambertian(b, checker)));
+    return s.finish({13, 2, 3}, {0, 0, 0}, 20.0, aspect, 0.0, 10.0, RTW_BG_GRADIENT);
+}
+
 }  // namespace
 
 extern "C" int rtw_build_named_scene(rtw_builder* b, const char* name, double aspect, const uint8_t* earth, int enx,
@@ -226,6 +259,8 @@ extern "C" int rtw_build_named_scene(rtw_builder* b, const char* name, double as
     else if (n == "cornell_box_aluminum") ok = cornell_box_scene(b, aspect, true);
     else if (n == "two_perlin_spheres_earth") ok = two_perlin_spheres_earth(b, aspect, earth, enx, eny);
     else if (n == "book2_final_scene") ok = book2_final_scene(b, aspect, earth, enx, eny);
+    else if (n == "cornell_smoke_scene") ok = cornell_smoke_scene(b, aspect);
+    else if (n == "checker_spheres_scene") ok = checker_spheres_scene(b, aspect);
     else {
         rtw::set_error("unknown scene name: " + n);
         return RTW_ERR_INVALID;

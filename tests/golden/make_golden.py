@@ -32,11 +32,11 @@ SCENES = rtw.SCENE_NAMES
 ASPECT = 1.5
 SERIAL = {"cornell_box_scene": (32, 32, 4), "cornell_box_aluminum": (24, 24, 4), "dielectric_scene": (32, 16, 4),
           "random_balls_scene": (24, 16, 2), "light_sample": (24, 24, 4), "two_perlin_spheres_earth": (24, 24, 4),
-          "book2_final_scene": (24, 24, 4)}
+          "book2_final_scene": (24, 24, 4), "cornell_smoke_scene": (24, 24, 4), "checker_spheres_scene": (24, 24, 4)}
 # converged images: (nx, ny, spp)
 IMAGES = {"cornell_box_scene": (64, 64, 4096), "cornell_box_aluminum": (64, 64, 4096), "dielectric_scene": (64, 32, 2048),
           "random_balls_scene": (48, 32, 1024), "light_sample": (48, 48, 2048), "two_perlin_spheres_earth": (48, 48, 2048),
-          "book2_final_scene": (48, 48, 2048)}
+          "book2_final_scene": (48, 48, 2048), "cornell_smoke_scene": (48, 48, 4096), "checker_spheres_scene": (48, 48, 1024)}
 
 
 def fixed_rays(builder, n: int, seed: int) -> np.ndarray:
@@ -65,6 +65,10 @@ def builder_for(name: str, aspect: float):
 
 
 def main():
+    only = [a.split("=", 1)[1].split(",") for a in sys.argv if a.startswith("--only=")]
+    global SCENES
+    if only:  # regenerate the per-scene files of these scenes only (flat_sha256.json is merged)
+        SCENES = tuple(only[0])
     assert ol.have_ref(), "build oracle/_ref/ref_harness first (make -C oracle ref)"
     earth_jpg = "/root/reference/RayTracingWeekend/earth.jpg"
     if os.path.exists(earth_jpg):
@@ -72,10 +76,14 @@ def main():
         a = np.asarray(Image.open(earth_jpg).convert("RGB"), dtype=np.uint8)
         a.tofile(os.path.join(HERE, "earth_256x256_rgb8.bin"))
         print("earth sha256", hashlib.sha256(a.tobytes()).hexdigest())
-    np.savez_compressed(os.path.join(HERE, "funcs.npz"), funcs=ol.ref_funcs(), perlin=ol.ref_perlin())
-    with open(os.path.join(HERE, "kat.json"), "w") as f:
-        json.dump(json.loads(ol.ref_run(["kat"])), f, indent=1)
-    sha = {s: hashlib.sha256(ol.ref_flat(s, ASPECT)).hexdigest() for s in SCENES}
+    if not only:
+        np.savez_compressed(os.path.join(HERE, "funcs.npz"), funcs=ol.ref_funcs(), perlin=ol.ref_perlin())
+        with open(os.path.join(HERE, "kat.json"), "w") as f:
+            json.dump(json.loads(ol.ref_run(["kat"])), f, indent=1)
+    sha = {}
+    if only and os.path.exists(os.path.join(HERE, "flat_sha256.json")):
+        sha = json.load(open(os.path.join(HERE, "flat_sha256.json")))
+    sha.update({s: hashlib.sha256(ol.ref_flat(s, ASPECT)).hexdigest() for s in SCENES})
     with open(os.path.join(HERE, "flat_sha256.json"), "w") as f:
         json.dump(sha, f, indent=1)
     for s in SCENES:

@@ -100,7 +100,8 @@ def test_intersect_batch_edge_cases(scenes):
 @pytest.mark.parametrize("scene,nx,ny,spp", [("cornell_box_aluminum", 48, 48, 8), ("cornell_box_scene", 40, 40, 8),
                                              ("dielectric_scene", 48, 24, 8), ("random_balls_scene", 36, 24, 4),
                                              ("light_sample", 32, 32, 8), ("two_perlin_spheres_earth", 32, 32, 8),
-                                             ("book2_final_scene", 32, 32, 4)])
+                                             ("book2_final_scene", 32, 32, 4), ("cornell_smoke_scene", 40, 40, 8),
+                                             ("checker_spheres_scene", 48, 32, 8)])
 def test_render_path_by_path_vs_oracle_philox(scenes, scene, nx, ny, spp):
     """Same Philox counters, same uniforms: the FP32 kernel must follow the FP64 oracle path for path.  A path may
     legitimately diverge when a branch decision (u < p, hit/miss at an edge) flips under FP32 rounding, so the test
@@ -111,7 +112,7 @@ def test_render_path_by_path_vs_oracle_philox(scenes, scene, nx, ny, spp):
     g = acc[..., :3].astype(np.float64)
     assert np.all(acc[..., 3] == spp)
     close = np.isclose(g, osum, rtol=2e-3, atol=1e-3 * spp).all(axis=2)
-    limit = {"book2_final_scene": 0.90, "random_balls_scene": 0.95}.get(scene, 0.97)
+    limit = {"book2_final_scene": 0.90, "random_balls_scene": 0.95, "cornell_smoke_scene": 0.90}.get(scene, 0.97)
     assert close.mean() >= limit, f"{close.mean():.4f} of pixels path-exact"
     assert abs(st["rays"] - orays) / orays < 0.02
     # unbiasedness of the divergent remainder: image means agree
@@ -283,3 +284,15 @@ def test_upload_time_trees_do_not_change_hits_or_images():
     a, sa = sah.render(32, 32, 4, seed=3)
     c, sc_ = ref.render(32, 32, 4, seed=3)
     assert sa["rays"] == sc_["rays"] and np.array_equal(a, c)
+
+
+def test_auto_flag_picks_the_design_from_scene_features(scenes):
+    AUTO = rtw._lib.RTW_FLAG_AUTO
+    b, sc = scenes("cornell_box_aluminum", 1.0)
+    _, st = sc.render(32, 32, 4, seed=1, flags=AUTO)
+    assert st["kernel_launches"] == 1  # constant textures, no media: megakernel
+    b, sc = scenes("two_perlin_spheres_earth", 1.0)
+    acc, st = sc.render(32, 32, 4, seed=1, flags=AUTO)
+    assert st["kernel_launches"] > 2  # noise + image textures: wavefront
+    ref, _ = sc.render(32, 32, 4, seed=1)
+    assert np.allclose(acc, ref, rtol=2e-2, atol=4e-3)
