@@ -296,3 +296,21 @@ def test_auto_flag_picks_the_design_from_scene_features(scenes):
     assert st["kernel_launches"] > 2  # noise + image textures: wavefront
     ref, _ = sc.render(32, 32, 4, seed=1)
     assert np.allclose(acc, ref, rtol=2e-2, atol=4e-3)
+
+
+def test_command_line_driver_writes_the_same_image(tmp_path):
+    """python -m raytracingweekend_b200: run-time scene / size / spp selection (replaces RayTracingWeekend.cpp:32-36, 199-202)."""
+    import subprocess
+    import sys
+    out = tmp_path / "c.p6"
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "raytracingweekend_b200", "--scene", "cornell_box_scene", "--nx", "40", "--ny", "24",
+                        "--spp", "8", "--seed", "4", "--out", str(out)], cwd=root, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    assert "Trace:" in r.stdout and "Write:" in r.stdout
+    sc = rtw.Scene.named("cornell_box_scene", 40 / 24)
+    acc, _ = sc.render(40, 24, 8, seed=4)
+    want = (np.float32(255.99).astype(np.float64) * rtw.tonemap(acc)[::-1]).astype(np.int64)
+    raw = out.read_bytes()
+    head = b"P6\n40 24\n255\n"
+    assert raw.startswith(head) and np.array_equal(np.frombuffer(raw[len(head):], dtype=np.uint8).reshape(24, 40, 3), want)
