@@ -698,8 +698,8 @@ int check_params(const rtw_scene* s, const rtw_render_params* p) {
         return RTW_ERR_INVALID;
     }
     if (p->nx <= 0 || p->ny <= 0 || p->spp_count <= 0 || p->spp_begin < 0 || p->max_depth < 0 ||
-        (long long)p->nx * p->ny > 0x7fffffffLL) {
-        set_error("render: bad nx/ny/spp/max_depth");
+        (long long)p->nx * p->ny > 0x7fffffffLL || p->spp_count > (1 << 26)) {  // a warp's pool holds 32*spp items
+        set_error("render: bad nx/ny/spp/max_depth (spp_count per launch <= 2^26)");
         return RTW_ERR_INVALID;
     }
     return RTW_OK;
@@ -721,6 +721,7 @@ extern "C" int rtw_render_device(rtw_scene* s, const rtw_render_params* p, float
     rp.nx = p->nx, rp.ny = p->ny, rp.spp_begin = p->spp_begin, rp.spp_count = p->spp_count, rp.max_depth = p->max_depth;
     rp.flags = p->flags;
     rp.seed_lo = (uint32_t)(p->seed & 0xffffffffu), rp.seed_hi = (uint32_t)(p->seed >> 32);
+    philox_round_keys(rp);
     if ((e = cudaMemsetAsync(s->d_counter, 0, sizeof(unsigned long long), st)) != cudaSuccess) return cuda_fail(e, "memset");
     if ((e = cudaEventRecord(s->ev0, st)) != cudaSuccess) return cuda_fail(e, "event");
     int launches = 1;

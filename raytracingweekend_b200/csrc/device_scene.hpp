@@ -138,7 +138,14 @@ struct DevRenderParams {
     int32_t nx, ny, spp_begin, spp_count, max_depth;
     uint32_t flags;
     uint32_t seed_lo, seed_hi;
+    uint32_t rk[20];  // Philox4x32-10 round keys of the seed: rk[2i] = seed_lo + i*0x9E3779B9, rk[2i+1] = seed_hi + i*0xBB67AE85
 };
+inline void philox_round_keys(DevRenderParams& rp) {
+    for (uint32_t i = 0; i < 10; i++) {
+        rp.rk[2 * i] = rp.seed_lo + i * 0x9E3779B9u;
+        rp.rk[2 * i + 1] = rp.seed_hi + i * 0xBB67AE85u;
+    }
+}
 
 // Where the blob lives for this block: `sbase` = 32-bit shared address of the staged prefix, `g` = global copy.
 struct SceneView {

@@ -54,23 +54,25 @@ struct Ray {  // ray.h:17-20 — direction is NOT normalised
 struct U4 {
     float x, y, z, w;
 };
-RTW_DEV uint4 philox4x32_10(uint4 c, uint2 k) {
-    const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+// `rk` = the ten round keys (seed + i * Weyl constants), computed once per launch on the host (DevRenderParams::rk):
+// they sit in the kernel-parameter constant bank and feed the round's LOP3 directly, which takes the 18 key-schedule
+// adds out of every draw.
+RTW_DEV uint4 philox4x32_10(uint4 c, const uint32_t* __restrict__ rk) {
+    const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u;
 #pragma unroll
     for (int i = 0; i < 10; i++) {
         uint32_t hi0 = __umulhi(M0, c.x), lo0 = M0 * c.x;
         uint32_t hi1 = __umulhi(M1, c.z), lo1 = M1 * c.z;
-        c = make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
-        k.x += W0;
-        k.y += W1;
+        c = make_uint4(hi1 ^ c.y ^ rk[2 * i], lo1, hi0 ^ c.w ^ rk[2 * i + 1], lo0);
     }
     return c;
 }
 RTW_DEV float u01(uint32_t x) { return (float)(x >> 8) * 5.9604644775390625e-8f; }  // 2^-24
 struct Rng {
-    uint32_t pixel, sample, seed_lo, seed_hi;
+    uint32_t pixel, sample;
+    const uint32_t* rk;  // DevRenderParams::rk of this launch
     RTW_DEV U4 draw(uint32_t bounce, uint32_t site) const {
-        uint4 r = philox4x32_10(make_uint4(pixel, sample, bounce, site), make_uint2(seed_lo, seed_hi));
+        uint4 r = philox4x32_10(make_uint4(pixel, sample, bounce, site), rk);
         return U4{u01(r.x), u01(r.y), u01(r.z), u01(r.w)};
     }
 };

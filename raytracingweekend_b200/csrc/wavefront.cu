@@ -71,7 +71,7 @@ RTW_DEV void wf_start_path(const DevScene& sc, const DevRenderParams& rp, const 
     }
     if (rp.flags & RTW_FLAG_DEBUG_RAY) gi = rp.nx / 2, gj = rp.ny / 2;  // RayTracingWeekend.cpp:221-225
     Rng rng;
-    rng.pixel = pixel, rng.sample = sample, rng.seed_lo = rp.seed_lo, rng.seed_hi = rp.seed_hi;
+    rng.pixel = pixel, rng.sample = sample, rng.rk = rp.rk;
     const Ray ray = camera_ray(sc, rp, rng, gi, gj);
     wp.A[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.time);
     wp.B[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(pixel));
@@ -107,7 +107,7 @@ __global__ void __launch_bounds__(kWfBlock) wf_extend(const __grid_constant__ De
                 const float4 a = wp.A[slot];
                 const uint32_t sb = __float_as_uint(wp.C[slot].w);
                 Rng rng;
-                rng.pixel = pixel, rng.sample = sb >> 8, rng.seed_lo = rp.seed_lo, rng.seed_hi = rp.seed_hi;
+                rng.pixel = pixel, rng.sample = sb >> 8, rng.rk = rp.rk;
                 const uint32_t bounce = (sb & 0xffu) + 1u;
                 // :52 world.hit(r, 0.001f, DBL_MAX, rec)
                 const HitId h = closest_hit<F, SM, false>(sc, sv, mk(a.x, a.y, a.z), mk(b.x, b.y, b.z), a.w, 0.001f, FLT_MAX, &rng,
@@ -174,7 +174,7 @@ __global__ void __launch_bounds__(kWfBlock) wf_shade(const __grid_constant__ Dev
         const float4 a = wp.A[slot], b = wp.B[slot], cc = wp.C[slot], d = wp.D[slot];
         const uint32_t pixel = __float_as_uint(b.w), sb = __float_as_uint(cc.w);
         Rng rng;
-        rng.pixel = pixel, rng.sample = sb >> 8, rng.seed_lo = rp.seed_lo, rng.seed_hi = rp.seed_hi;
+        rng.pixel = pixel, rng.sample = sb >> 8, rng.rk = rp.rk;
         const uint32_t bounce = (sb & 0xffu) + 1u;
         Ray ray;
         ray.o = mk(a.x, a.y, a.z), ray.d = mk(b.x, b.y, b.z), ray.time = a.w;

@@ -71,6 +71,18 @@ def main():
     for (f, ln), v in sorted(lines.items(), key=lambda kv: -kv[1][3])[:top]:
         thr = v[2] / v[1] if v[1] else 0
         print(f"{f + ':' + str(ln):26s} {100 * v[1] / tot_inst:6.2f} {100 * v[3] / tot_samp:6.2f} {thr:5.1f}  {v[0][:110]}")
+    # where the divergence is: warp instructions (issue slots) by how many lanes were active on their source line
+    buckets = [[0, 0, 0] for _ in range(4)]
+    for v in lines.values():
+        if v[1]:
+            b = min(3, int(v[2] / v[1] / 8.0))
+            buckets[b][0] += v[1]
+            buckets[b][1] += v[2]
+            buckets[b][2] += v[3]
+    print(f"\n{'active lanes':14s} {'inst%':>6s} {'samp%':>6s} {'thread-inst%':>13s}")
+    tot_t = sum(b[1] for b in buckets) or 1
+    for k, b in enumerate(buckets):
+        print(f"{8 * k:3d}-{8 * k + 8:<10d} {100 * b[0] / tot_inst:6.2f} {100 * b[2] / tot_samp:6.2f} {100 * b[1] / tot_t:13.2f}")
     print(f"\n{'opcode':12s} {'inst%':>6s} {'samp%':>6s} {'thr':>5s}")
     for name, (i, t, s) in sorted(ops.items(), key=lambda kv: -kv[1][0])[:30]:
         print(f"{name:12s} {100 * i / tot_inst:6.2f} {100 * s / tot_samp:6.2f} {t / i if i else 0:5.1f}")
