@@ -754,8 +754,11 @@ extern "C" int rtw_render_device(rtw_scene* s, const rtw_render_params* p, float
         if ((e = launch_wavefront(s->dev, rp, (float4*)accum_dev, s->d_counter, s->wf_scratch, s->wf_slots, s->wf_host_flag, &launches, st)) !=
             cudaSuccess)
             return cuda_fail(e, "wavefront launch");
-    } else if ((e = launch_render(s->dev, rp, (float4*)accum_dev, s->d_counter, st)) != cudaSuccess) {
-        return cuda_fail(e, "render launch");
+    } else {
+        static const bool use_sorted = [] { const char* v = getenv("RTW_MEGA_SORTED"); return v && atoi(v) != 0; }();
+        if (use_sorted && sorted_supports(rp)) e = launch_render_sorted(s->dev, rp, (float4*)accum_dev, s->d_counter, st);
+        else e = launch_render(s->dev, rp, (float4*)accum_dev, s->d_counter, st);
+        if (e != cudaSuccess) return cuda_fail(e, "render launch");
     }
     if ((e = cudaEventRecord(s->ev1, st)) != cudaSuccess) return cuda_fail(e, "event");
     s->pending = true;

@@ -13,6 +13,11 @@ uint32_t pick_variant(uint32_t features);
 cudaError_t launch_render(const DevScene& sc, const DevRenderParams& rp, float4* accum, unsigned long long* ray_counter,
                           cudaStream_t st);
 
+// Megakernel with material-sorted shading (sorted.cu): same contract; `sorted_supports` = its packing limits.
+bool sorted_supports(const DevRenderParams& rp);
+cudaError_t launch_render_sorted(const DevScene& sc, const DevRenderParams& rp, float4* accum, unsigned long long* ray_counter,
+                                 cudaStream_t st);
+
 cudaError_t launch_intersect(const DevScene& sc, const rtw_ray* rays, rtw_hit* hits, long long n, float tmin, float tmax,
                              cudaStream_t st);
 

@@ -14,10 +14,13 @@ namespace rtw {
 // wavefront pipeline runs the two halves in different kernels.
 template <uint32_t F, int SM>
 RTW_DEV bool shade_hit(const DevScene& sc, const SceneView& sv, const Rng& rng, uint32_t bounce, const HitId& h, Ray& ray,
-                       V3& beta, V3& L) {
+                       V3& beta, V3& L, bool need_main = true) {
     // The bounce's main uniforms are drawn here, before control flow diverges by material: every lane of the
     // warp runs the ten Philox rounds together instead of once per material branch.
-    U4 rmain = rng.draw(bounce, SITE_MAIN);
+    // `need_main` = false (warp-uniform) when the caller already knows that no lane consumes them (sorted.cu: units of
+    // metal, isotropic or terminal hits).
+    U4 rmain = U4{0.0f, 0.0f, 0.0f, 0.0f};
+    if (need_main) rmain = rng.draw(bounce, SITE_MAIN);
     if (h.prim == -1) {  // :141-159
         L = L + beta * background(sc, ray.d);
         return false;

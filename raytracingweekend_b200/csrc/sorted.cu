@@ -1,0 +1,279 @@
+// sorted.cu — the megakernel with material-sorted shading (sm_100a).
+//
+// The lane-owns-a-path megakernel (kernels.cu) traverses at ~31 of 32 lanes but shades at 3-15: after the hit a warp
+// holds a mix of lambertian, dielectric, metal and terminal events and runs every branch.  Here the path state lives in
+// shared memory instead of registers, and the warps of a block exchange paths through per-class queues so that a
+// warp always shades 32 paths of ONE material class and then traces their 32 new rays:
+//
+//   block  = 256 threads, one 16x16 pixel tile, one pool of (pixel, sample) items like the warp pool of kernels.cu
+//   slots  = kSPool path slots in shared memory, 64 B each: (o, t) (d, time) (beta, prim) (item, pixel, sample, bounce)
+//   queues = one ring of slot ids per class in shared memory {lambertian, dielectric, metal, isotropic, terminal
+//            (miss / emitter), needs-a-camera-ray}; producers reserve with one atomicAdd per (warp, class) found by
+//            match_any, consumers claim 32 entries with a CAS on the head.  No block-wide barrier after start-up.
+//   unit   = claim 32 entries of one class -> load state -> shade_hit (coherent) -> new ray -> closest_hit (full
+//            lanes) -> classify -> store state -> push.  Terminal units add their radiance and start 32 new camera
+//            rays on the spot, so camera maths also runs at full lanes.
+//
+// Per-pixel sums are 64-bit fixed point (2^-24) in shared memory: integer adds commute, so the image stays
+// bit-reproducible although units run in a timing-dependent order.  Samples that are not finite or >= 8192 go to a
+// float side accumulator (NaN / Inf propagate like in the reference).  HBM traffic is unchanged: one 16-byte
+// store per pixel per launch.
+#include "kernels.hpp"
+#include "rt_path.cuh"
+#include "rt_stage.cuh"
+
+namespace rtw {
+
+constexpr int kSBlock = 256;
+#ifndef RTW_SORTED_PER_THREAD
+#define RTW_SORTED_PER_THREAD 3
+#endif
+constexpr int kSPool = kSBlock * RTW_SORTED_PER_THREAD;
+constexpr int kSTile = 16;  // 16 x 16 pixels per block
+constexpr int kSPix = kSTile * kSTile;
+#ifndef RTW_SORTED_MIN_BLOCKS
+#define RTW_SORTED_MIN_BLOCKS 3
+#endif
+
+enum : int { C_LAMB = 0, C_DIEL, C_METAL, C_ISO, C_TERM, C_REGEN, C_QUEUES, C_DEAD = C_QUEUES };
+constexpr int kQCap = 1024;  // ring capacity per class (power of two >= kSPool)
+constexpr uint16_t kQEmpty = 0xffffu;
+static_assert(kSPool <= kQCap, "queue rings must hold every slot");
+
+struct SortedCtl {
+    unsigned int head[8], tail[8];  // per class ring: [head, tail) are queued entries (tail = reserved)
+    unsigned int item_next;         // the block's (pixel, sample) pool
+    int live;                       // slots that still carry or may get a path
+};
+
+size_t sorted_pool_bytes() {
+    return (size_t)kSPool * 64 + (size_t)C_QUEUES * kQCap * 2 + (size_t)kSPix * 3 * (8 + 4) + sizeof(SortedCtl) + 64;
+}
+
+template <uint32_t F, int SM>
+__global__ void __launch_bounds__(kSBlock, RTW_SORTED_MIN_BLOCKS) render_sorted(const __grid_constant__ DevScene sc,
+                                                                              const __grid_constant__ DevRenderParams rp,
+                                                                              float4* __restrict__ accum,
+                                                                              unsigned long long* __restrict__ ray_counter,
+                                                                              uint32_t pool_off) {
+    extern __shared__ uint4 smem[];
+    const SceneView sv = stage_scene<SM>(sc, smem);
+    int* stack = stack_base(sc, SM, smem) + threadIdx.x;
+    // pool carve-up (pool_off = staged bytes + stacks, 16-byte aligned by the host)
+    uint8_t* base = reinterpret_cast<uint8_t*>(smem) + pool_off;
+    float4* stA = reinterpret_cast<float4*>(base);  // o.xyz, t
+    float4* stB = stA + kSPool;                     // d.xyz, time
+    float4* stC = stB + kSPool;                     // beta.xyz, prim
+    uint4* stD = reinterpret_cast<uint4*>(stC + kSPool);  // item, global pixel index, sample, bounce | pixel slot << 16
+    unsigned long long* fx = reinterpret_cast<unsigned long long*>(stD + kSPool);  // [3][kSPix] fixed-point sums
+    float* fl = reinterpret_cast<float*>(fx + 3 * kSPix);                           // [3][kSPix] side sums
+    volatile uint16_t* queue = reinterpret_cast<volatile uint16_t*>(fl + 3 * kSPix);  // [C_QUEUES][kQCap]
+    SortedCtl* ctl = reinterpret_cast<SortedCtl*>(const_cast<uint16_t*>(queue) + C_QUEUES * kQCap);
+    volatile unsigned int* vhead = ctl->head;
+    volatile unsigned int* vtail = ctl->tail;
+
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int tiles_x = (rp.nx + kSTile - 1) / kSTile;
+    const int x0 = (blockIdx.x % tiles_x) * kSTile, y0 = (blockIdx.x / tiles_x) * kSTile;
+    const int w_in = min(kSTile, rp.nx - x0), h_in = min(kSTile, rp.ny - y0);
+    const int n_pix = w_in * h_in;  // > 0 for every launched block
+    const bool full_tile = n_pix == kSPix;
+    const uint32_t total = (uint32_t)n_pix * (uint32_t)rp.spp_count;  // < 2^31 (host check: spp_count <= 2^23)
+
+    // pixel slot -> pixel: full tiles use an 8x4-blocked order so that 32 consecutive items are a compact tile
+    auto slot_pixel = [&](uint32_t sl, int& pi, int& pj) {
+        if (full_tile) {
+            pi = x0 + (int)((sl & 7u) | ((sl >> 2) & 8u));
+            pj = y0 + (int)(((sl >> 3) & 3u) | ((sl >> 4) & 12u));
+        } else {
+            const int row = (int)sl / w_in;
+            pj = y0 + row, pi = x0 + (int)sl - row * w_in;
+        }
+    };
+
+    for (int k = tid; k < 3 * kSPix; k += kSBlock) fx[k] = 0ull, fl[k] = 0.0f;
+    for (int k = tid; k < C_QUEUES * kQCap; k += kSBlock) queue[k] = kQEmpty;
+    __syncthreads();
+    for (int s = tid; s < kSPool; s += kSBlock) queue[C_REGEN * kQCap + s] = (uint16_t)s;  // every slot needs a camera ray
+    if (tid < 8) ctl->head[tid] = 0, ctl->tail[tid] = (tid == C_REGEN) ? kSPool : 0;
+    if (tid == 8) ctl->item_next = 0, ctl->live = kSPool;
+    __syncthreads();
+
+    Rng rng;
+    rng.rk = rp.rk;
+    unsigned long long rays = 0;
+    for (;;) {
+        // ---- claim a unit: 32 entries of the first class (in cost order) that has them, else the longest partial run
+        int c = -1, n = 0;
+        unsigned int h = 0;
+        if (lane == 0) {
+            int spins = 0;
+            for (;;) {
+                int best = -1, best_n = 0;
+                unsigned int best_h = 0;
+#pragma unroll
+                for (int k = 0; k < C_QUEUES; k++) {
+                    const unsigned int hk = vhead[k];
+                    const int avail = (int)(vtail[k] - hk);
+                    if (avail > best_n && best_n < 32) best = k, best_n = min(avail, 32), best_h = hk;
+                }
+                if (best < 0) {
+                    if (*(volatile int*)&ctl->live <= 0) break;
+                    __nanosleep(200);
+                    continue;
+                }
+                if (best_n < 32 && spins < 2) {  // others are mid-unit: give them a moment to fill a whole unit
+                    spins++;
+                    __nanosleep(300);
+                    continue;
+                }
+                if (atomicCAS(&ctl->head[best], best_h, best_h + (unsigned int)best_n) == best_h) {
+                    c = best, n = best_n, h = best_h;
+                    break;
+                }
+            }
+        }
+        c = __shfl_sync(0xffffffffu, c, 0);
+        if (c < 0) break;
+        n = __shfl_sync(0xffffffffu, n, 0);
+        h = __shfl_sync(0xffffffffu, h, 0);
+        const bool valid = lane < n;
+        const unsigned vmask = __ballot_sync(0xffffffffu, valid);
+        int slot = 0;
+        Ray ray;
+        ray.o = ray.d = mk(0.0f, 0.0f, 0.0f);
+        ray.time = 0.0f;
+        V3 beta = mk(1.0f, 1.0f, 1.0f);
+        uint32_t pix = 0, bounce = 0;
+        bool alive = false;
+        if (valid) {
+            volatile uint16_t* e = queue + c * kQCap + ((h + lane) & (kQCap - 1));
+            uint16_t sv16;
+            while ((sv16 = *e) == kQEmpty) {}  // reserved by a producer that has not written it yet
+            *e = kQEmpty;
+            slot = sv16;
+            __threadfence_block();  // the entry was published after the slot's state
+            if (c <= C_TERM) {      // warp-uniform
+                const float4 a = stA[slot], b = stB[slot], cc = stC[slot];
+                const uint4 d = stD[slot];
+                ray.o = mk(a.x, a.y, a.z), ray.d = mk(b.x, b.y, b.z), ray.time = b.w;
+                beta = mk(cc.x, cc.y, cc.z);
+                HitId hit;
+                hit.t = a.w, hit.prim = fi(cc.w), hit.item = (int)d.x;
+                rng.pixel = d.y, rng.sample = d.z;
+                bounce = d.w & 0xffffu, pix = d.w >> 16;
+                V3 L = mk(0.0f, 0.0f, 0.0f);
+                alive = shade_hit<F, SM>(sc, sv, rng, bounce, hit, ray, beta, L, c == C_LAMB || c == C_DIEL);
+                if (alive && (int)bounce >= rp.max_depth) alive = false;  // :47-48: the next color() returns 0
+                if (!alive) {                                             // :235-239
+                    const float v[3] = {L.x, L.y, L.z};
+#pragma unroll
+                    for (int ch = 0; ch < 3; ch++) {
+                        if (v[ch] != 0.0f) {
+                            if (fabsf(v[ch]) < 8192.0f)
+                                atomicAdd(fx + ch * kSPix + pix, (unsigned long long)__float2ll_rn(v[ch] * 16777216.0f));
+                            else
+                                atomicAdd(fl + ch * kSPix + pix, v[ch]);
+                        }
+                    }
+                }
+            }
+        }
+        if (c >= C_TERM) {  // warp-uniform: every valid lane needs a new path
+            unsigned int item = 0;
+            if (lane == 0) item = atomicAdd(&ctl->item_next, (unsigned int)n);
+            item = __shfl_sync(0xffffffffu, item, 0) + lane;
+            if (valid && item < total) {
+                uint32_t sm;
+                if (full_tile) sm = item >> 8, pix = item & 255u;
+                else sm = item / (uint32_t)n_pix, pix = item - sm * (uint32_t)n_pix;
+                int pi, pj;
+                slot_pixel(pix, pi, pj);
+                rng.pixel = (uint32_t)(pj * rp.nx + pi);
+                rng.sample = (uint32_t)rp.spp_begin + sm;  // global sample index: shards are disjoint streams
+                if (rp.flags & RTW_FLAG_DEBUG_RAY) pi = rp.nx / 2, pj = rp.ny / 2;  // RayTracingWeekend.cpp:221-225
+                ray = camera_ray(sc, rp, rng, pi, pj);
+                beta = mk(1.0f, 1.0f, 1.0f);
+                bounce = 0;
+                alive = true;
+            }
+        }
+        __syncwarp();
+        int ncls = (c >= C_TERM) ? C_DEAD : C_REGEN;  // a terminal/regen lane only stays dead when the pool is empty
+        if (alive) {
+            bounce++;
+            rays++;
+            const HitId hit = closest_hit<F, SM, false>(sc, sv, ray.o, ray.d, ray.time, 0.001f, FLT_MAX, &rng, bounce, stack, kSBlock);
+            ncls = C_TERM;
+            if (hit.prim != -1 && sc.render_type != RTW_RENDER_NORMAL) {
+                uint32_t pm;
+                const int mat_idx = hit_material<SM>(sc, sv, hit, pm);
+                const int mt = ld_mat<SM>(sv, sc.off[SEC_MATS] + (uint32_t)mat_idx * 32u).type;
+                ncls = mt == RTW_MAT_DIFFUSE_LIGHT ? C_TERM
+                       : mt == RTW_MAT_METAL       ? C_METAL
+                       : mt == RTW_MAT_DIELECTRIC  ? C_DIEL
+                       : mt == RTW_MAT_ISOTROPIC   ? C_ISO
+                                                   : C_LAMB;
+            }
+            stA[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, hit.t);
+            stB[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, ray.time);
+            stC[slot] = make_float4(beta.x, beta.y, beta.z, __int_as_float(hit.prim));
+            stD[slot] = make_uint4((uint32_t)hit.item, rng.pixel, rng.sample, bounce | (pix << 16));
+            __threadfence_block();  // state before the queue entry
+        }
+        if (valid) {
+            const unsigned same = __match_any_sync(vmask, ncls);
+            const int leader = __ffs(same) - 1;
+            unsigned int pos = 0;
+            if (lane == leader) {
+                if (ncls != C_DEAD) pos = atomicAdd(&ctl->tail[ncls], (unsigned int)__popc(same));
+                else atomicSub(&ctl->live, __popc(same));
+            }
+            pos = __shfl_sync(vmask, pos, leader);
+            if (ncls != C_DEAD) queue[ncls * kQCap + ((pos + __popc(same & ((1u << lane) - 1u))) & (kQCap - 1))] = (uint16_t)slot;
+        }
+    }
+    __syncthreads();
+
+    // one 16-byte store per pixel (canvas[j*nx+i], RayTracingWeekend.cpp:247)
+    for (int p = tid; p < n_pix; p += kSBlock) {
+        int pi, pj;
+        slot_pixel((uint32_t)p, pi, pj);
+        const size_t idx = (size_t)pj * rp.nx + pi;
+        float4 out;
+        out.x = (float)((double)(long long)fx[p] * (1.0 / 16777216.0)) + fl[p];
+        out.y = (float)((double)(long long)fx[kSPix + p] * (1.0 / 16777216.0)) + fl[kSPix + p];
+        out.z = (float)((double)(long long)fx[2 * kSPix + p] * (1.0 / 16777216.0)) + fl[2 * kSPix + p];
+        out.w = (float)rp.spp_count;
+        if (rp.flags & RTW_FLAG_ACCUMULATE) {
+            const float4 prev = accum[idx];
+            out.x += prev.x, out.y += prev.y, out.z += prev.z, out.w += prev.w;
+        }
+        accum[idx] = out;
+    }
+    for (int o = 16; o > 0; o >>= 1) rays += __shfl_down_sync(0xffffffffu, rays, o);
+    if (lane == 0 && rays) atomicAdd(ray_counter, rays);
+}
+
+namespace {
+template <uint32_t F, int SM>
+cudaError_t launch_sorted_t(const DevScene& sc, const DevRenderParams& rp, float4* accum, unsigned long long* counter,
+                            size_t smem, cudaStream_t st) {
+    const int tiles_x = (rp.nx + kSTile - 1) / kSTile, tiles_y = (rp.ny + kSTile - 1) / kSTile;
+    const uint32_t pool_off = (uint32_t)((smem + 15) & ~(size_t)15);
+    const size_t bytes = pool_off + sorted_pool_bytes();
+    cudaError_t e = cudaFuncSetAttribute(render_sorted<F, SM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    if (e != cudaSuccess) return e;
+    render_sorted<F, SM><<<tiles_x * tiles_y, kSBlock, bytes, st>>>(sc, rp, accum, counter, pool_off);
+    return cudaGetLastError();
+}
+}  // namespace
+
+bool sorted_supports(const DevRenderParams& rp) { return rp.spp_count <= (1 << 23) && rp.max_depth < (1 << 24); }
+
+cudaError_t launch_render_sorted(const DevScene& sc, const DevRenderParams& rp, float4* accum, unsigned long long* counter,
+                                 cudaStream_t st) {
+    RTW_DISPATCH(kSBlock, launch_sorted_t, sc, rp, accum, counter);
+}
+
+}  // namespace rtw
