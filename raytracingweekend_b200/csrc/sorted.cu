@@ -18,6 +18,8 @@
 // bit-reproducible although units run in a timing-dependent order.  Samples that are not finite or >= 8192 go to a
 // float side accumulator (NaN / Inf propagate like in the reference).  HBM traffic is unchanged: one 16-byte
 // store per pixel per launch.
+#include <cstdio>
+
 #include "kernels.hpp"
 #include "rt_path.cuh"
 #include "rt_stage.cuh"
@@ -40,6 +42,9 @@ constexpr int kQCap = 1024;  // ring capacity per class (power of two >= kSPool)
 constexpr uint16_t kQEmpty = 0xffffu;
 static_assert(kSPool <= kQCap, "queue rings must hold every slot");
 
+#ifdef RTW_SORTED_STATS
+__device__ int g_stats[8][2];
+#endif
 struct SortedCtl {
     unsigned int head[8], tail[8];  // per class ring: [head, tail) are queued entries (tail = reserved)
     unsigned int item_next;         // the block's (pixel, sample) pool
@@ -102,43 +107,51 @@ __global__ void __launch_bounds__(kSBlock, RTW_SORTED_MIN_BLOCKS) render_sorted(
     Rng rng;
     rng.rk = rp.rk;
     unsigned long long rays = 0;
+    const int pref = (tid >> 5) % C_TERM;  // the class this warp looks at first: one of the four scatter classes
     for (;;) {
-        // ---- claim a unit: 32 entries of the first class (in cost order) that has them, else the longest partial run
+        // ---- claim a unit: 32 entries of a class that has them (each warp starts looking at a different class, which
+        // spreads the CAS traffic), else - after a short wait for the warps that are mid-unit - the longest partial run.
+        // Lanes 0..5 each look at one queue.
         int c = -1, n = 0;
         unsigned int h = 0;
-        if (lane == 0) {
-            int spins = 0;
-            for (;;) {
-                int best = -1, best_n = 0;
-                unsigned int best_h = 0;
-#pragma unroll
-                for (int k = 0; k < C_QUEUES; k++) {
-                    const unsigned int hk = vhead[k];
-                    const int avail = (int)(vtail[k] - hk);
-                    if (avail > best_n && best_n < 32) best = k, best_n = min(avail, 32), best_h = hk;
-                }
-                if (best < 0) {
+        for (int spins = 0;;) {
+            unsigned int hk = 0;
+            int avail = 0;
+            if (lane < C_QUEUES) hk = vhead[lane], avail = (int)(vtail[lane] - hk);
+            const unsigned full = __ballot_sync(0xffffffffu, avail >= 32);
+            int k;
+            if (full) {
+                const unsigned from_pref = full & ~((1u << pref) - 1u);
+                k = __ffs(from_pref ? from_pref : full) - 1;
+                n = 32;
+            } else {
+                const unsigned best = __reduce_max_sync(0xffffffffu, (unsigned)(max(avail, 0) << 3) | (unsigned)(lane & 7));
+                if ((best >> 3) == 0) {  // nothing queued anywhere
                     if (*(volatile int*)&ctl->live <= 0) break;
                     __nanosleep(200);
                     continue;
                 }
-                if (best_n < 32 && spins < 2) {  // others are mid-unit: give them a moment to fill a whole unit
+                if (spins < 2) {
                     spins++;
                     __nanosleep(300);
                     continue;
                 }
-                if (atomicCAS(&ctl->head[best], best_h, best_h + (unsigned int)best_n) == best_h) {
-                    c = best, n = best_n, h = best_h;
-                    break;
-                }
+                k = (int)(best & 7u), n = (int)(best >> 3);
+            }
+            h = __shfl_sync(0xffffffffu, hk, k);
+            int ok = 0;
+            if (lane == 0) ok = atomicCAS(&ctl->head[k], h, h + (unsigned int)n) == h;
+            if (__shfl_sync(0xffffffffu, ok, 0)) {
+                c = k;
+                break;
             }
         }
-        c = __shfl_sync(0xffffffffu, c, 0);
         if (c < 0) break;
-        n = __shfl_sync(0xffffffffu, n, 0);
-        h = __shfl_sync(0xffffffffu, h, 0);
         const bool valid = lane < n;
         const unsigned vmask = __ballot_sync(0xffffffffu, valid);
+#ifdef RTW_SORTED_STATS
+        if (lane == 0 && blockIdx.x == 1000) atomicAdd(&g_stats[c][0], 1), atomicAdd(&g_stats[c][1], n);
+#endif
         int slot = 0;
         Ray ray;
         ray.o = ray.d = mk(0.0f, 0.0f, 0.0f);
@@ -179,6 +192,7 @@ __global__ void __launch_bounds__(kSBlock, RTW_SORTED_MIN_BLOCKS) render_sorted(
                 }
             }
         }
+        __syncwarp();       // reconverge the lanes that added radiance with those that did not
         if (c >= C_TERM) {  // warp-uniform: every valid lane needs a new path
             unsigned int item = 0;
             if (lane == 0) item = atomicAdd(&ctl->item_next, (unsigned int)n);
@@ -234,6 +248,10 @@ __global__ void __launch_bounds__(kSBlock, RTW_SORTED_MIN_BLOCKS) render_sorted(
         }
     }
     __syncthreads();
+#ifdef RTW_SORTED_STATS
+    if (tid == 0 && blockIdx.x == 1000)
+        for (int k = 0; k < C_QUEUES; k++) printf("class %d: units %d lanes %d\n", k, g_stats[k][0], g_stats[k][1]);
+#endif
 
     // one 16-byte store per pixel (canvas[j*nx+i], RayTracingWeekend.cpp:247)
     for (int p = tid; p < n_pix; p += kSBlock) {
