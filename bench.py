@@ -34,6 +34,7 @@ SPP = 1024
 MAX_DEPTH = 100
 # SURVEY §8d / DESIGN.md §5: algorithmic FP32 flops per path of the reference's math on this scene, counted by the
 # instrumented oracle (tools/count_flops.py: oracle_events_*, 64x64x64 spp sample, Appendix D cost table).
+NCU_DRAM_BYTES_PER_LAUNCH = 117504 + 236032  # read + write, see roofline.traffic below
 FLOP_PER_PATH = 1344.5
 FP32_PEAK_SPEC_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12  # 74.4
 
@@ -277,12 +278,20 @@ def run_ours(args) -> None:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     except Exception:
         pass
+    sorted_kernel = os.environ.get("RTW_MEGA_SORTED", "1") != "0"
     roofline = {"bound": "fp32-issue", "achieved": achieved, "peak": peak.value, "unit": "TFLOP/s",
-                "frac": achieved / peak.value if peak.value else None, "traffic": None,
+                "frac": achieved / peak.value if peak.value else None,
+                # dram__bytes_read.sum + dram__bytes_write.sum of ONE full-size (1024 spp, whole image) launch, from the ncu
+                # --set full capture summarised in profiles/r1_sorted_cornell_ncu_details.txt; the 16 MB image was still
+                # in L2 when the kernel ended.  Only valid for the single-GPU shape of that capture.
+                "traffic": NCU_DRAM_BYTES_PER_LAUNCH if world == 1 and sorted_kernel else None,
+                "traffic_unit": "bytes per launch (ncu, profiles/r1_sorted_cornell_ncu_details.txt)",
                 "peak_source": "FFMA micro-benchmark run in this process (rtw_measure_fp32_peak); spec-derived "
                                f"{FP32_PEAK_SPEC_TFLOPS:.1f} TFLOP/s at 1965 MHz",
                 "frac_of_spec": achieved / FP32_PEAK_SPEC_TFLOPS,
-                "algorithmic_flop_per_path": fpp, "kernel": "render_megakernel", "kernel_ms_per_launch": kern_ms / args.steps,
+                "algorithmic_flop_per_path": fpp,
+                "kernel": "render_sorted (material-sorted megakernel, csrc/sorted.cu)" if sorted_kernel else "render_megakernel",
+                "kernel_ms_per_launch": kern_ms / args.steps,
                 "hbm": {"algorithmic_bytes_per_launch": NX * NY * 16, "achieved_gbs": NX * NY * 16 / (kern_ms / args.steps * 1e-3) / 1e9,
                         "peak_gbs": peaks.get("hbm_gbs"), "note": "not HBM-bound: one 16-byte store per pixel per launch"}}
     cpu = cpu_reference(15.0) if world == 1 else None

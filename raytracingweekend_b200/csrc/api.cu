@@ -667,9 +667,17 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
     d.n_world_items = fs->n_world_items, d.n_items = fs->n_items, d.n_prims = fs->n_prims, d.n_lights = fs->n_lights;
     d.render_type = fs->render_type, d.background_type = fs->background_type;
     d.features = feat, d.max_bvh_depth = max_depth;
-    for (int i = 0; i < fs->n_textures; i++)
-        if (fs->textures[i].type == RTW_TEX_NOISE) s->prefer_wavefront = true;
-    if ((feat & F_MEDIA) && fs->n_nodes > 0) s->prefer_wavefront = true;
+    // RTW_FLAG_AUTO: the multi-kernel wavefront pipeline beat the lane-owns-a-path megakernel on noise-textured and on
+    // media + BVH scenes; the material-sorted megakernel is faster than both on every measured class, so
+    // AUTO only falls back to the wavefront rule when the sorted kernel is switched off.
+    {
+        const char* v = getenv("RTW_MEGA_SORTED");
+        if (v && atoi(v) == 0) {
+            for (int i = 0; i < fs->n_textures; i++)
+                if (fs->textures[i].type == RTW_TEX_NOISE) s->prefer_wavefront = true;
+            if ((feat & F_MEDIA) && fs->n_nodes > 0) s->prefer_wavefront = true;
+        }
+    }
     const rtw_flat_camera& c = fs->camera;
     DevCamera& k = d.cam;
     k.ox = (float)c.origin[0], k.oy = (float)c.origin[1], k.oz = (float)c.origin[2];
@@ -755,7 +763,8 @@ extern "C" int rtw_render_device(rtw_scene* s, const rtw_render_params* p, float
             cudaSuccess)
             return cuda_fail(e, "wavefront launch");
     } else {
-        static const bool use_sorted = [] { const char* v = getenv("RTW_MEGA_SORTED"); return v && atoi(v) != 0; }();
+        // the material-sorted megakernel (sorted.cu) is the default; RTW_MEGA_SORTED=0 selects the warp-pool kernel
+        static const bool use_sorted = [] { const char* v = getenv("RTW_MEGA_SORTED"); return !v || atoi(v) != 0; }();
         if (use_sorted && sorted_supports(rp)) e = launch_render_sorted(s->dev, rp, (float4*)accum_dev, s->d_counter, st);
         else e = launch_render(s->dev, rp, (float4*)accum_dev, s->d_counter, st);
         if (e != cudaSuccess) return cuda_fail(e, "render launch");

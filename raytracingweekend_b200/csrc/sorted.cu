@@ -27,20 +27,17 @@
 namespace rtw {
 
 constexpr int kSBlock = 256;
-#ifndef RTW_SORTED_PER_THREAD
-#define RTW_SORTED_PER_THREAD 3
-#endif
-constexpr int kSPool = kSBlock * RTW_SORTED_PER_THREAD;
 constexpr int kSTile = 16;  // 16 x 16 pixels per block
 constexpr int kSPix = kSTile * kSTile;
-#ifndef RTW_SORTED_MIN_BLOCKS
-#define RTW_SORTED_MIN_BLOCKS 3
-#endif
+// PT = path slots per thread.  The pool size trades queue fill (whole 32-path units per class) against resident blocks:
+// PT = 2 -> 512 slots, 49 KB, 4 blocks/SM at <= 64 registers (small kernels: the Cornell-class variant, +7 % there);
+// PT = 3 -> 768 slots, 71 KB, 3 blocks/SM at <= 80 registers (texture / BVH / media variants, which spill at 64).
+__host__ __device__ constexpr int pool_slots(int pt) { return kSBlock * pt; }
+__host__ __device__ constexpr int queue_cap(int pt) { return pool_slots(pt) <= 512 ? 512 : 1024; }  // ring capacity per class (power of two >= slots)
+__host__ __device__ constexpr int min_blocks(int pt) { return pt <= 2 ? 4 : (pt == 3 ? 3 : 2); }
 
 enum : int { C_LAMB = 0, C_DIEL, C_METAL, C_ISO, C_TERM, C_REGEN, C_QUEUES, C_DEAD = C_QUEUES };
-constexpr int kQCap = 1024;  // ring capacity per class (power of two >= kSPool)
 constexpr uint16_t kQEmpty = 0xffffu;
-static_assert(kSPool <= kQCap, "queue rings must hold every slot");
 
 #ifdef RTW_SORTED_STATS
 __device__ int g_stats[8][2];
@@ -51,16 +48,17 @@ struct SortedCtl {
     int live;                       // slots that still carry or may get a path
 };
 
-size_t sorted_pool_bytes() {
-    return (size_t)kSPool * 64 + (size_t)C_QUEUES * kQCap * 2 + (size_t)kSPix * 3 * (8 + 4) + sizeof(SortedCtl) + 64;
+constexpr size_t sorted_pool_bytes(int pt) {
+    return (size_t)pool_slots(pt) * 64 + (size_t)C_QUEUES * queue_cap(pt) * 2 + (size_t)kSPix * 3 * (8 + 4) + sizeof(SortedCtl) + 64;
 }
 
-template <uint32_t F, int SM>
-__global__ void __launch_bounds__(kSBlock, RTW_SORTED_MIN_BLOCKS) render_sorted(const __grid_constant__ DevScene sc,
+template <uint32_t F, int SM, int PT>
+__global__ void __launch_bounds__(kSBlock, min_blocks(PT)) render_sorted(const __grid_constant__ DevScene sc,
                                                                               const __grid_constant__ DevRenderParams rp,
                                                                               float4* __restrict__ accum,
                                                                               unsigned long long* __restrict__ ray_counter,
                                                                               uint32_t pool_off) {
+    constexpr int kSPool = pool_slots(PT), kQCap = queue_cap(PT);
     extern __shared__ uint4 smem[];
     const SceneView sv = stage_scene<SM>(sc, smem);
     int* stack = stack_base(sc, SM, smem) + threadIdx.x;
@@ -277,12 +275,13 @@ namespace {
 template <uint32_t F, int SM>
 cudaError_t launch_sorted_t(const DevScene& sc, const DevRenderParams& rp, float4* accum, unsigned long long* counter,
                             size_t smem, cudaStream_t st) {
+    constexpr int PT = (F == kVariants[0]) ? 2 : 3;
     const int tiles_x = (rp.nx + kSTile - 1) / kSTile, tiles_y = (rp.ny + kSTile - 1) / kSTile;
     const uint32_t pool_off = (uint32_t)((smem + 15) & ~(size_t)15);
-    const size_t bytes = pool_off + sorted_pool_bytes();
-    cudaError_t e = cudaFuncSetAttribute(render_sorted<F, SM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    const size_t bytes = pool_off + sorted_pool_bytes(PT);
+    cudaError_t e = cudaFuncSetAttribute(render_sorted<F, SM, PT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
     if (e != cudaSuccess) return e;
-    render_sorted<F, SM><<<tiles_x * tiles_y, kSBlock, bytes, st>>>(sc, rp, accum, counter, pool_off);
+    render_sorted<F, SM, PT><<<tiles_x * tiles_y, kSBlock, bytes, st>>>(sc, rp, accum, counter, pool_off);
     return cudaGetLastError();
 }
 }  // namespace
