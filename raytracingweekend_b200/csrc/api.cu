@@ -219,12 +219,39 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
     // Built with INDICES first; converted to blob byte offsets once the section offsets are known (below).
     std::vector<DevGroup> groups;
     std::vector<DevRec> recs;
+    // The six rects emitted for a reference `box` (builder.cpp K_BOX: xy z1, xy z0, xz y1, xz y0, yz x1, yz x0 over the
+    // same extents): detected here so that they get a group of their own with a box record (device_scene.hpp).
+    static const bool use_boxes = [] { const char* v = getenv("RTW_BOX_PRIMS"); return !v || atoi(v) != 0; }();
+    auto is_box_at = [&](const std::vector<int>& ids, size_t q, size_t end) {
+        if (!use_boxes || q + 6 > end) return false;
+        const rtw_flat_prim* P[6];
+        for (int k = 0; k < 6; k++) {
+            if (ids[q + k] != ids[q] + k) return false;
+            P[k] = &fs->prims[ids[q + k]];
+        }
+        const int want[6] = {RTW_PRIM_XY_RECT, RTW_PRIM_XY_RECT, RTW_PRIM_XZ_RECT, RTW_PRIM_XZ_RECT, RTW_PRIM_YZ_RECT, RTW_PRIM_YZ_RECT};
+        for (int k = 0; k < 6; k++)
+            if (P[k]->type != want[k]) return false;
+        const double x0 = P[0]->v[0], x1 = P[0]->v[1], y0 = P[0]->v[2], y1 = P[0]->v[3], z1 = P[0]->v[4], z0 = P[1]->v[4];
+        if (!(x0 < x1 && y0 < y1 && z0 < z1)) return false;
+        auto same = [](const rtw_flat_prim* a, double a0, double a1, double b0, double b1, double k) {
+            return a->v[0] == a0 && a->v[1] == a1 && a->v[2] == b0 && a->v[3] == b1 && a->v[4] == k;
+        };
+        return same(P[1], x0, x1, y0, y1, z0) && same(P[2], x0, x1, z0, z1, y1) && same(P[3], x0, x1, z0, z1, y0) &&
+               same(P[4], y0, y1, z0, z1, x1) && same(P[5], y0, y1, z0, z1, x0);
+    };
     auto add_groups_of = [&](const std::vector<int>& ids, int& first_group, int& end_group) {
         first_group = (int)groups.size();
         size_t i = 0;
         while (i < ids.size()) {
+            // a run = consecutive primitives with one transform chain, cut so that a box is a run of its own
             size_t j = i;
-            while (j < ids.size() && fs->prims[ids[j]].xf == fs->prims[ids[i]].xf) j++;
+            bool box = is_box_at(ids, i, ids.size());
+            if (box) {
+                j = i + 6;
+            } else {
+                while (j < ids.size() && fs->prims[ids[j]].xf == fs->prims[ids[i]].xf && !is_box_at(ids, j, ids.size())) j++;
+            }
             DevGroup g{};
             g.xf = fs->prims[ids[i]].xf;
             g.sph0 = (int)recs.size();
@@ -252,6 +279,18 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
                 }
                 *ends[k] = (int)recs.size();
             }
+            if (box) {
+                const rtw_flat_prim& xy1r = fs->prims[ids[i]];      // x0 x1 y0 y1 | z1
+                const rtw_flat_prim& xy0r = fs->prims[ids[i + 1]];  // z0
+                const rtw_flat_prim& xz1r = fs->prims[ids[i + 2]];  // x0 x1 z0 z1 | y1
+                DevRec r{};
+                // the same FP32 constants as the rect records (round to nearest), so t is bit-identical to the rect test
+                r.a = make_float4((float)xy1r.v[0], (float)xy1r.v[2], (float)xy0r.v[4], 0.0f);
+                r.b = make_float4((float)xy1r.v[1], (float)xy1r.v[3], (float)xy1r.v[4], __int_as_float_host(ids[i]));
+                (void)xz1r;
+                recs.push_back(r);
+            }
+            g.box1 = (int)recs.size();
             groups.push_back(g);
             i = j;
         }
@@ -616,7 +655,7 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
     for (DevGroup& g : groups) {
         g.xf = xf_off(g.xf);
         g.sph0 = rec_off(g.sph0), g.sph1 = rec_off(g.sph1), g.msph1 = rec_off(g.msph1);
-        g.xy1 = rec_off(g.xy1), g.xz1 = rec_off(g.xz1), g.yz1 = rec_off(g.yz1);
+        g.xy1 = rec_off(g.xy1), g.xz1 = rec_off(g.xz1), g.yz1 = rec_off(g.yz1), g.box1 = rec_off(g.box1);
     }
     for (DevItem& d : items) {
         d.xf = xf_off(d.xf);

@@ -50,14 +50,18 @@ struct DevItem {
 };
 
 // Run of primitive-test records sharing one transform chain.  All members are byte offsets into the blob:
-// [sph0, sph1) spheres; [sph1, msph1) moving spheres; [msph1, xy1) xy_rects; [xy1, xz1) xz_rects; [xz1, yz1) yz_rects.
+// [sph0, sph1) spheres; [sph1, msph1) moving spheres; [msph1, xy1) xy_rects; [xy1, xz1) xz_rects; [xz1, yz1) yz_rects;
+// [yz1, box1) box records.  The six rects of a reference `box` (hittable_list.h:69-104) form a group of their own
+// that ALSO carries one box record: the render kernels run one slab test instead of six rect tests (same t expression,
+// same winning face = same primitive id), intersect_batch keeps the rect-by-rect order of the reference.
 struct DevGroup {
     int32_t xf;  // byte offset of the DevXf, or -1
     int32_t sph0, sph1, msph1;
-    int32_t xy1, xz1, yz1, pad;
+    int32_t xy1, xz1, yz1, box1;
 };
 
 // One primitive-test record (32 bytes = two 16-byte loads).
+//   box:           a = (lo.x, lo.y, lo.z, -)       b = (hi.x, hi.y, hi.z, id of the first of its six rect prims)
 //   sphere:        a = (cx, cy, cz, radius)        b = (pd index bits, -, -, prim id | REC_PRECISE)
 //   moving sphere: a = (c'x, c'y, c'z, radius)     b = (dx, dy, dz, prim id)     centre(time) = c' + time*d
 //   rect:          a = (a0, a1, b0, b1)            b = (k, -, -, prim id)

@@ -362,14 +362,48 @@ RTW_DEV float4 hot4_abs(const SceneView& sv, uint32_t addr) {
     return v;
 }
 
-// The five kind loops of one group, for ray constants `k` already in the group's frame.
-template <uint32_t F, int SM>
+// One slab test for the six rects of a reference `box` (hittable_list.h:69-104; record layout in device_scene.hpp).
+// The nearest of the six rect hits with t in [tmin, t_best] is the entry face if the ray starts before it, else the
+// exit face; t = (k - o_n) * inv_n is the expression of rect_update, so the winner's t is bit-identical.  The rect ids are
+// id0 + {0: z = hi, 1: z = lo, 2: y = hi, 3: y = lo, 4: x = hi, 5: x = lo} (builder.cpp K_BOX).
+RTW_DEV void box_update(float4 lo, float4 hi, const RayK& k, float tmin, float& t_best, int& prim_best) {
+    const float tx0 = (lo.x - k.o.x) * k.inv.x, tx1 = (hi.x - k.o.x) * k.inv.x;
+    const float ty0 = (lo.y - k.o.y) * k.inv.y, ty1 = (hi.y - k.o.y) * k.inv.y;
+    const float tz0 = (lo.z - k.o.z) * k.inv.z, tz1 = (hi.z - k.o.z) * k.inv.z;
+    const float nx = fminf(tx0, tx1), fx = fmaxf(tx0, tx1);
+    const float ny = fminf(ty0, ty1), fy = fmaxf(ty0, ty1);
+    const float nz = fminf(tz0, tz1), fz = fmaxf(tz0, tz1);
+    const float te = fmaxf(fmaxf(nx, ny), nz), tf = fminf(fminf(fx, fy), fz);
+    const bool entry = te >= tmin;
+    const float t = entry ? te : tf;
+    if (te <= tf && t >= tmin && t <= t_best) {
+        // the face: the axis that produced t; on that axis the lo plane is the near one iff t?0 <= t?1
+        const float ax = entry ? nx : fx, ay = entry ? ny : fy;
+        const bool on_x = ax == t, on_y = ay == t;
+        const bool lo_near = on_x ? (tx0 <= tx1) : (on_y ? (ty0 <= ty1) : (tz0 <= tz1));
+        const int axis_base = on_x ? 4 : (on_y ? 2 : 0);
+        t_best = t;
+        prim_best = fi(hi.w) + axis_base + ((lo_near == entry) ? 1 : 0);
+    }
+}
+
+// The five kind loops of one group, for ray constants `k` already in the group's frame.  BOXREC (render kernels): a group
+// that carries a box record is tested with it instead of its six rects.
+template <uint32_t F, int SM, bool BOXREC>
 RTW_DEV void test_group_kinds(const SceneView& sv, float4 g0, float4 g1, const RayK& k, float time, float tmin, float& t_best,
                               int& prim_best) {
     const uint32_t sph0 = hot_abs<SM>(sv, (uint32_t)fi(g0.y)), sph1 = hot_abs<SM>(sv, (uint32_t)fi(g0.z));
     const uint32_t msph1 = hot_abs<SM>(sv, (uint32_t)fi(g0.w));
     const uint32_t xy1 = hot_abs<SM>(sv, (uint32_t)fi(g1.x)), xz1 = hot_abs<SM>(sv, (uint32_t)fi(g1.y));
     const uint32_t yz1 = hot_abs<SM>(sv, (uint32_t)fi(g1.z));
+    if (BOXREC) {
+        const uint32_t box1 = hot_abs<SM>(sv, (uint32_t)fi(g1.w));
+        if (box1 != yz1) {  // warp-uniform
+#pragma unroll 1
+            for (uint32_t r = yz1; r < box1; r += 32) box_update(hot4_abs<SM>(sv, r), hot4_abs<SM>(sv, r + 16), k, tmin, t_best, prim_best);
+            return;
+        }
+    }
 #pragma unroll 1
     for (uint32_t r = sph0; r < sph1; r += 32) {
         float4 ra = hot4_abs<SM>(sv, r), rb = hot4_abs<SM>(sv, r + 16);
@@ -417,19 +451,24 @@ RTW_DEV void test_group_kinds(const SceneView& sv, float4 g0, float4 g1, const R
     }
 }
 
-template <uint32_t F, int SM>
+template <uint32_t F, int SM, bool BOXREC>
 RTW_DEV void test_groups(const SceneView& sv, uint32_t gfirst, uint32_t gend, const RayK& rk, float time, float tmin,
                          float& t_best, int& prim_best) {
     const uint32_t ga0 = hot_abs<SM>(sv, gfirst), ga1 = hot_abs<SM>(sv, gend);
 #pragma unroll 1
     for (uint32_t ga = ga0; ga < ga1; ga += 32) {
         const float4 g0 = hot4_abs<SM>(sv, ga), g1 = hot4_abs<SM>(sv, ga + 16);
-        // two instantiations of the kind loops instead of `k = xf ? xf_rayk(rk) : rk`: no 11-register copy per group
-        if ((F & F_XF) && fi(g0.x) >= 0) {
+        // two instantiations of the kind loops instead of `k = xf ? xf_rayk(rk) : rk`: no 11-register copy per group.
+        // The all-features variant keeps ONE copy: its kernels are > 100 KB of SASS and instruction-cache bound.
+        if constexpr ((F & F_MEDIA) != 0) {
+            RayK k = rk;
+            if ((F & F_XF) && fi(g0.x) >= 0) k = xf_rayk(ld_xf<SM>(sv, (uint32_t)fi(g0.x)), rk);
+            test_group_kinds<F, SM, BOXREC>(sv, g0, g1, k, time, tmin, t_best, prim_best);
+        } else if ((F & F_XF) && fi(g0.x) >= 0) {
             const RayK k = xf_rayk(ld_xf<SM>(sv, (uint32_t)fi(g0.x)), rk);
-            test_group_kinds<F, SM>(sv, g0, g1, k, time, tmin, t_best, prim_best);
+            test_group_kinds<F, SM, BOXREC>(sv, g0, g1, k, time, tmin, t_best, prim_best);
         } else {
-            test_group_kinds<F, SM>(sv, g0, g1, rk, time, tmin, t_best, prim_best);
+            test_group_kinds<F, SM, BOXREC>(sv, g0, g1, rk, time, tmin, t_best, prim_best);
         }
     }
 }

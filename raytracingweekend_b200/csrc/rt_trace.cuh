@@ -21,7 +21,7 @@ namespace rtw {
 // that hold one test their leaves together, so node steps and primitive tests do not serialise against each other.
 // Stack: shared memory, one column per thread (`stack[level * stride]`).
 constexpr int kBvhDone = (int)0x80000000;  // not a valid reference: ~0x7fffffff is never a leaf offset
-template <uint32_t F, int SM, bool SHRINK, bool FAST_BOX>
+template <uint32_t F, int SM, bool SHRINK, bool FAST_BOX, bool BOXREC>
 RTW_DEV void bvh_hit(const SceneView& sv, int root, const RayK& rk, float time, float tmin, float tmax, int* stack,
                      int stride, float& t_out, int& prim_out) {
     const V3 o = rk.o, inv = rk.inv;
@@ -58,7 +58,7 @@ RTW_DEV void bvh_hit(const SceneView& sv, int root, const RayK& rk, float time, 
             const uint2 lf = hot2<SM>(sv, (uint32_t)~ref);
             float t_leaf = tmax;
             int p_leaf = -1;
-            test_groups<F, SM>(sv, lf.x, lf.y, rk, time, tmin, t_leaf, p_leaf);
+            test_groups<F, SM, BOXREC>(sv, lf.x, lf.y, rk, time, tmin, t_leaf, p_leaf);
             const int leaf = ~ref;
             if (p_leaf >= 0 && (best_prim < 0 || t_leaf < best || (t_leaf == best && leaf >= best_leaf))) {
                 best = t_leaf;
@@ -104,7 +104,7 @@ RTW_DEV HitId closest_hit(const DevScene& sc, const SceneView& sv, V3 o, V3 d, f
         const int type = fi(i0.x), ixf = fi(i0.y), first = fi(i0.z), end = fi(i0.w);
         if (kOnlyLists || type == RTW_ITEM_PRIMS) {
             int before = h.prim;
-            test_groups<F, SM>(sv, (uint32_t)first, (uint32_t)end, rk, time, tmin, h.t, h.prim);
+            test_groups<F, SM, !EXACT_TIES>(sv, (uint32_t)first, (uint32_t)end, rk, time, tmin, h.t, h.prim);
             if (h.prim != before) h.item = it;
         } else if ((F & F_BVH) && type == RTW_ITEM_BVH) {
             RayK lk = rk;
@@ -112,7 +112,7 @@ RTW_DEV HitId closest_hit(const DevScene& sc, const SceneView& sv, V3 o, V3 d, f
             int p = -1;
             float t = h.t;
             // intersect_batch walks the reference's own topology (`first`), rendering the SAH tree over the same leaves (`end`)
-            bvh_hit<F, SM, true, RTW_FAST_BOX && !EXACT_TIES>(sv, EXACT_TIES ? first : end, lk, time, tmin, h.t, stack, stride, t, p);
+            bvh_hit<F, SM, true, RTW_FAST_BOX && !EXACT_TIES, !EXACT_TIES>(sv, EXACT_TIES ? first : end, lk, time, tmin, h.t, stack, stride, t, p);
             if (p >= 0) {
                 h.t = t;
                 h.prim = p;
@@ -125,13 +125,20 @@ RTW_DEV HitId closest_hit(const DevScene& sc, const SceneView& sv, V3 o, V3 d, f
             RayK lk = rk;
             if (ixf >= 0) lk = xf_rayk(ld_xf<SM>(sv, (uint32_t)ixf), rk);
             float t1 = FLT_MAX, t2 = FLT_MAX;
-            int p1 = -1, p2 = -1;
-            test_groups<F, SM>(sv, (uint32_t)first, (uint32_t)end, lk, time, -FLT_MAX, t1, p1);  // :438-442
-            if (p1 < 0) continue;
-            // :447 `rec1.t + 0.0001f`; in FP32 the step can vanish for |t| > ~800, so advance at least one ulp
-            float step = fmaxf(t1 + 0.0001f, nextafterf(t1, FLT_MAX));
-            test_groups<F, SM>(sv, (uint32_t)first, (uint32_t)end, lk, time, step, t2, p2);  // :445-449
-            if (p2 < 0) continue;
+            // the two boundary searches (:438-442, :445-449) share one call site (code size): pass 1 starts at
+            // `rec1.t + 0.0001f` (:447); in FP32 that step can vanish for |t| > ~800, so advance at least one ulp
+            bool both = false;
+#pragma unroll 1
+            for (int pass = 0; pass < 2; pass++) {
+                float tb = FLT_MAX;
+                int pb = -1;
+                const float from = pass == 0 ? -FLT_MAX : fmaxf(t1 + 0.0001f, nextafterf(t1, FLT_MAX));
+                test_groups<F, SM, !EXACT_TIES>(sv, (uint32_t)first, (uint32_t)end, lk, time, from, tb, pb);
+                if (pb < 0) break;
+                if (pass == 0) t1 = tb;
+                else t2 = tb, both = true;
+            }
+            if (!both) continue;
             if (t1 < tmin) t1 = tmin;  // :452-457
             if (t2 > h.t) t2 = h.t;
             if (t1 >= t2) continue;
@@ -155,14 +162,14 @@ RTW_DEV HitId closest_hit(const DevScene& sc, const SceneView& sv, V3 o, V3 d, f
             const int type = fi(i0.x), ixf = fi(i0.y), first = fi(i0.z), end = fi(i0.w);
             if (type == RTW_ITEM_PRIMS) {
                 int before = h.prim;
-                test_groups<F, SM>(sv, (uint32_t)first, (uint32_t)end, rk, time, tmin, h.t, h.prim);
+                test_groups<F, SM, false>(sv, (uint32_t)first, (uint32_t)end, rk, time, tmin, h.t, h.prim);
                 if (h.prim != before) h.item = it;
             } else if (type == RTW_ITEM_BVH) {
                 RayK lk = rk;
                 if (ixf >= 0) lk = xf_rayk(ld_xf<SM>(sv, (uint32_t)ixf), rk);
                 int p = -1;
                 float t = h.t;
-                bvh_hit<F, SM, false, false>(sv, first, lk, time, tmin, h.t, stack, stride, t, p);
+                bvh_hit<F, SM, false, false, false>(sv, first, lk, time, tmin, h.t, stack, stride, t, p);
                 if (p >= 0) {
                     h.t = t;
                     h.prim = p;
