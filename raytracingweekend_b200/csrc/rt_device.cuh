@@ -218,7 +218,7 @@ RTW_DEV bool sphere_roots(V3 oc, V3 d, float a, float inv_a, float radius, float
     return true;
 }
 template <int SM>
-RTW_DEV bool sphere_roots_f64(const SceneView& sv, uint32_t pd_off, V3 o, V3 d, float& t0, float& t1) {
+RTW_DEV bool sphere_roots_f64(const SceneView& sv, uint32_t pd_off, V3 o, V3 d, float inv_a, float& t0, float& t1) {
     double cx = cold_f64<SM>(sv, pd_off), cy = cold_f64<SM>(sv, pd_off + 8), cz = cold_f64<SM>(sv, pd_off + 16);
     double rad = cold_f64<SM>(sv, pd_off + 24);
     double ocx = (double)o.x - cx, ocy = (double)o.y - cy, ocz = (double)o.z - cz;
@@ -228,9 +228,11 @@ RTW_DEV bool sphere_roots_f64(const SceneView& sv, uint32_t pd_off, V3 o, V3 d, 
     double c = ocx * ocx + ocy * ocy + ocz * ocz - rad * rad;
     double disc = b * b - a * c;
     if (!(disc > 0.0)) return false;
+    // FP64 only where FP32 cancels (b*b - a*c and -b -+ sq for |r| >= 100); the division by a = d.d is the ray's FP32
+    // reciprocal (2 ulp), which keeps two inlined FP64 divisions out of every copy of the sphere loop
     double sq = sqrt(disc);
-    t0 = (float)((-b - sq) / a);
-    t1 = (float)((-b + sq) / a);
+    t0 = (float)(-b - sq) * inv_a;
+    t1 = (float)(-b + sq) * inv_a;
     return true;
 }
 // Pick the root the reference would return; false if neither lies in (tmin, tmax).
@@ -411,7 +413,7 @@ RTW_DEV void test_group_kinds(const SceneView& sv, float4 g0, float4 g1, const R
         float t0, t1, t;
         bool roots;
         if ((F & F_PRECISE) && (id & REC_PRECISE)) {
-            roots = sphere_roots_f64<SM>(sv, (uint32_t)fi(rb.x), k.o, k.d, t0, t1);
+            roots = sphere_roots_f64<SM>(sv, (uint32_t)fi(rb.x), k.o, k.d, k.inv_a, t0, t1);
             id &= ~REC_PRECISE;
         } else {
             roots = sphere_roots(k.o - mk(ra.x, ra.y, ra.z), k.d, k.a, k.inv_a, ra.w, t0, t1);

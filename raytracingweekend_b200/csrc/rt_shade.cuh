@@ -40,7 +40,8 @@ RTW_DEV float perlin_noise(const DevScene& sc, const SceneView& sv, V3 p) {
 template <int SM>
 RTW_DEV float perlin_turb(const DevScene& sc, const SceneView& sv, V3 p) {  // noise.h:74-86, depth 7
     float accum = 0.0f, weight = 1.0f;
-    for (int i = 0; i < 7; i++) {
+#pragma unroll 1
+    for (int i = 0; i < 7; i++) {  // rolled: seven unrolled octaves are 750 SASS instructions at every call site
         accum = fmaf(weight, perlin_noise<SM>(sc, sv, p), accum);
         weight *= 0.5f;
         p = p * 2.0f;
@@ -48,19 +49,30 @@ RTW_DEV float perlin_turb(const DevScene& sc, const SceneView& sv, V3 p) {  // n
     return fabsf(accum);
 }
 
+// sin(x) for texture arguments (|x| up to ~1e4): two-constant Cody-Waite reduction to [-pi, pi], then MUFU.SIN (2^-21
+// absolute there).  libdevice sinf is ~40 instructions plus a slow path per call site, and texture_value is inlined at
+// three call sites of shade_hit.
+RTW_DEV float sin_reduced(float x) {
+    const float k = rintf(x * 0.15915494309189535f);
+    float r = fmaf(-k, 6.28318548202514648f, x);   // 2*pi rounded to FP32
+    r = fmaf(-k, -1.74845553e-7f, r);              // 2*pi - fl(2*pi)
+    return __sinf(r);
+}
+
 // texture::value(u, v, p) (texture.h:21-24, 35-46, 57-68, 81-94)
 template <int SM>
 RTW_DEV V3 texture_value(const DevScene& sc, const SceneView& sv, int tex, float u, float v, V3 p) {
-    for (int guard = 0; guard < 16; guard++) {
+#pragma unroll 1
+    for (int guard = 0; guard < 16; guard++) {  // checker textures chain to their even/odd child
         DevTex t = ld_tex<SM>(sv, sc.off[SEC_TEXS] + (uint32_t)tex * 48u);
         if (t.type == RTW_TEX_CONSTANT) return mk(t.r, t.g, t.b);
         if (t.type == RTW_TEX_CHECKER) {
-            float sines = sinf(10.0f * p.x) * sinf(10.0f * p.y) * sinf(10.0f * p.z);
+            float sines = sin_reduced(10.0f * p.x) * sin_reduced(10.0f * p.y) * sin_reduced(10.0f * p.z);
             tex = (sines < 0.0f) ? t.odd : t.even;
             continue;
         }
         if (t.type == RTW_TEX_NOISE) {
-            float g = 0.5f * (1.0f + sinf(fmaf(t.scale, p.z, 10.0f * perlin_turb<SM>(sc, sv, p))));
+            float g = 0.5f * (1.0f + sin_reduced(fmaf(t.scale, p.z, 10.0f * perlin_turb<SM>(sc, sv, p))));
             return mk(g, g, g);
         }
         // image_texture (texture.h:81-94): nearest texel, v flipped
