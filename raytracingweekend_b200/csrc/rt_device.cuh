@@ -454,8 +454,8 @@ RTW_DEV void test_group_kinds(const SceneView& sv, float4 g0, float4 g1, const R
 }
 
 template <uint32_t F, int SM, bool BOXREC>
-RTW_DEV void test_groups(const SceneView& sv, uint32_t gfirst, uint32_t gend, const RayK& rk, float time, float tmin,
-                         float& t_best, int& prim_best) {
+RTW_DEV void test_groups_body(const SceneView& sv, uint32_t gfirst, uint32_t gend, const RayK& rk, float time, float tmin,
+                              float& t_best, int& prim_best) {
     const uint32_t ga0 = hot_abs<SM>(sv, gfirst), ga1 = hot_abs<SM>(sv, gend);
 #pragma unroll 1
     for (uint32_t ga = ga0; ga < ga1; ga += 32) {
@@ -472,6 +472,30 @@ RTW_DEV void test_groups(const SceneView& sv, uint32_t gfirst, uint32_t gend, co
         } else {
             test_group_kinds<F, SM, BOXREC>(sv, g0, g1, rk, time, tmin, t_best, prim_best);
         }
+    }
+}
+
+// The all-features kernels call ONE out-of-line copy of the primitive loops from their three call sites (world lists,
+// BVH leaves, medium boundaries): they are instruction-fetch bound (ncu: 42 % of stall samples `no_instruction` on the
+// Book-2 final scene with the loops inlined three times); the small variants keep them inline.
+struct GroupHit {
+    float t;
+    int prim;
+};
+template <uint32_t F, int SM, bool BOXREC>
+__device__ __noinline__ GroupHit test_groups_call(SceneView sv, uint32_t gfirst, uint32_t gend, RayK rk, float time, float tmin,
+                                                  float t_best, int prim_best) {
+    test_groups_body<F, SM, BOXREC>(sv, gfirst, gend, rk, time, tmin, t_best, prim_best);
+    return GroupHit{t_best, prim_best};
+}
+template <uint32_t F, int SM, bool BOXREC>
+RTW_DEV void test_groups(const SceneView& sv, uint32_t gfirst, uint32_t gend, const RayK& rk, float time, float tmin,
+                         float& t_best, int& prim_best) {
+    if constexpr ((F & F_MEDIA) != 0 && SM < 2) {  // big scenes only: a small staged scene (Cornell smoke) loses 19 % to the calls
+        const GroupHit g = test_groups_call<F, SM, BOXREC>(sv, gfirst, gend, rk, time, tmin, t_best, prim_best);
+        t_best = g.t, prim_best = g.prim;
+    } else {
+        test_groups_body<F, SM, BOXREC>(sv, gfirst, gend, rk, time, tmin, t_best, prim_best);
     }
 }
 
