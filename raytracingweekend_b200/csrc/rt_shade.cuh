@@ -86,9 +86,16 @@ RTW_DEV V3 texture_value(const DevScene& sc, const SceneView& sv, int tex, float
     return mk(0.0f, 0.0f, 0.0f);
 }
 
+// out-of-line copy for the big (unstaged) scenes, whose kernels are instruction-fetch bound: shade_hit evaluates textures
+// at three call sites (emitter, isotropic, lambertian)
+template <int SM>
+__device__ __noinline__ V3 texture_value_call(const DevScene* sc, SceneView sv, int tex, float u, float v, V3 p) {
+    return texture_value<SM>(*sc, sv, tex, u, v, p);
+}
 template <uint32_t F, int SM>
 RTW_DEV V3 material_texture(const DevScene& sc, const SceneView& sv, const DevMat& m, float u, float v, V3 p) {
     if (!(F & F_TEXTURES) || m.tex_is_constant) return mk(m.r, m.g, m.b);
+    if constexpr (SM < 2) return texture_value_call<SM>(&sc, sv, m.texture, u, v, p);
     return texture_value<SM>(sc, sv, m.texture, u, v, p);
 }
 

@@ -30,8 +30,10 @@ constexpr int kSBlock = 256;
 constexpr int kSTile = 16;  // 16 x 16 pixels per block
 constexpr int kSPix = kSTile * kSTile;
 // PT = path slots per thread.  The pool size trades queue fill (whole 32-path units per class) against resident blocks:
-// PT = 2 -> 512 slots, 49 KB, 4 blocks/SM at <= 64 registers (small kernels: the Cornell-class variant, +7 % there);
-// PT = 3 -> 768 slots, 71 KB, 3 blocks/SM at <= 80 registers (texture / BVH / media variants, which spill at 64).
+// PT = 2 -> 512 slots, 49 KB: 4 blocks/SM at <= 64 registers for the Cornell-class variant (+7 % there); 3 blocks/SM at
+//           80 registers for the BVH variants, whose traversal stacks take another 10-20 KB per block and which are
+//           latency-bound (Book-2 final +19 %, random balls +11 % over PT = 3 at 2 blocks/SM);
+// PT = 3 -> 768 slots, 71 KB, 3 blocks/SM at <= 80 registers (texture variant: it spills at 64 registers).
 __host__ __device__ constexpr int pool_slots(int pt) { return kSBlock * pt; }
 __host__ __device__ constexpr int queue_cap(int pt) { return pool_slots(pt) <= 512 ? 512 : 1024; }  // ring capacity per class (power of two >= slots)
 __host__ __device__ constexpr int min_blocks(int pt) { return pt <= 2 ? 4 : (pt == 3 ? 3 : 2); }
@@ -52,8 +54,8 @@ constexpr size_t sorted_pool_bytes(int pt) {
     return (size_t)pool_slots(pt) * 64 + (size_t)C_QUEUES * queue_cap(pt) * 2 + (size_t)kSPix * 3 * (8 + 4) + sizeof(SortedCtl) + 64;
 }
 
-template <uint32_t F, int SM, int PT>
-__global__ void __launch_bounds__(kSBlock, min_blocks(PT)) render_sorted(const __grid_constant__ DevScene sc,
+template <uint32_t F, int SM, int PT, int MB>
+__global__ void __launch_bounds__(kSBlock, MB) render_sorted(const __grid_constant__ DevScene sc,
                                                                               const __grid_constant__ DevRenderParams rp,
                                                                               float4* __restrict__ accum,
                                                                               unsigned long long* __restrict__ ray_counter,
@@ -275,13 +277,17 @@ namespace {
 template <uint32_t F, int SM>
 cudaError_t launch_sorted_t(const DevScene& sc, const DevRenderParams& rp, float4* accum, unsigned long long* counter,
                             size_t smem, cudaStream_t st) {
-    constexpr int PT = (F == kVariants[0]) ? 2 : 3;
+#ifndef RTW_SORTED_BVH_PT
+#define RTW_SORTED_BVH_PT 2
+#endif
+    constexpr int PT = (F == kVariants[0]) ? 2 : ((F & F_BVH) ? RTW_SORTED_BVH_PT : 3);
+    constexpr int MB = (F == kVariants[0]) ? 4 : ((F & F_BVH) && PT == 4 ? 2 : 3);
     const int tiles_x = (rp.nx + kSTile - 1) / kSTile, tiles_y = (rp.ny + kSTile - 1) / kSTile;
     const uint32_t pool_off = (uint32_t)((smem + 15) & ~(size_t)15);
     const size_t bytes = pool_off + sorted_pool_bytes(PT);
-    cudaError_t e = cudaFuncSetAttribute(render_sorted<F, SM, PT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    cudaError_t e = cudaFuncSetAttribute(render_sorted<F, SM, PT, MB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
     if (e != cudaSuccess) return e;
-    render_sorted<F, SM, PT><<<tiles_x * tiles_y, kSBlock, bytes, st>>>(sc, rp, accum, counter, pool_off);
+    render_sorted<F, SM, PT, MB><<<tiles_x * tiles_y, kSBlock, bytes, st>>>(sc, rp, accum, counter, pool_off);
     return cudaGetLastError();
 }
 }  // namespace
