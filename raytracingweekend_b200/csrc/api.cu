@@ -153,8 +153,11 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
         set_error("scene_create: null flat scene");
         return nullptr;
     }
+    // RTW_DRY_RUN=1 (diagnostics only): build the device-side tables without a device, print the RTW_DEBUG_TREES line, fail
+    const bool dry_run = getenv("RTW_DRY_RUN") != nullptr;
     int ndev = 0;
-    cudaError_t e = cudaGetDeviceCount(&ndev);
+    cudaError_t e = dry_run ? cudaSuccess : cudaGetDeviceCount(&ndev);
+    if (dry_run) ndev = device + 1;
     if (e != cudaSuccess || device < 0 || device >= ndev) {
         set_error(std::string("scene_create: no usable CUDA device (") + (e != cudaSuccess ? cudaGetErrorString(e) : "bad index") +
                   "); this backend has no CPU fallback");
@@ -162,11 +165,11 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
         return nullptr;
     }
     cudaDeviceProp prop;
-    if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess || prop.major != 10) {
+    if (!dry_run && ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess || prop.major != 10)) {
         set_error("scene_create: device is not compute capability 10.x (kernels are built for sm_100a only)");
         return nullptr;
     }
-    if ((e = cudaSetDevice(device)) != cudaSuccess) {
+    if (!dry_run && (e = cudaSetDevice(device)) != cudaSuccess) {
         cuda_fail(e, "cudaSetDevice");
         return nullptr;
     }
@@ -570,7 +573,91 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
         items[i] = d;
     }
     max_depth += 1;  // pseudo-root
-    if (max_depth > 60) {
+
+    // (3) the 4-wide render trees (DevNode4): every tree the render kernels walk (`DevItem.end`) is collapsed — a child that is an
+    // inner node is replaced by its own two children, largest box first, until the node holds four — so a ray fetches about
+    // half as many nodes, each one cache line.  Leaves (and with them the right-most-leaf tie rule) are untouched.
+    std::vector<DevNode4> nodes4;
+    int stack4_need = 0;
+    {
+        struct Child {
+            int ref;
+            float lo[3], hi[3];
+        };
+        auto children_of = [&](int b, std::vector<Child>& out, size_t at) {
+            const DevNode& n = nodes[b];
+            int l, r;
+            memcpy(&l, &n.llo.w, 4), memcpy(&r, &n.lhi.w, 4);
+            std::vector<Child> cs;
+            cs.push_back(Child{l, {n.llo.x, n.llo.y, n.llo.z}, {n.lhi.x, n.lhi.y, n.lhi.z}});
+            if (n.rlo.x <= n.rhi.x) cs.push_back(Child{r, {n.rlo.x, n.rlo.y, n.rlo.z}, {n.rhi.x, n.rhi.y, n.rhi.z}});
+            for (Child& c : cs)
+                if (b < fs->n_nodes && c.ref >= 0)  // a reference bvh_node's own (unpadded) box: pad it like the boxes built here
+                    for (int k = 0; k < 3; k++) {
+                        float m = std::max(std::fabs(c.lo[k]), std::fabs(c.hi[k])), pad = 1e-3f + 2e-5f * m;
+                        c.lo[k] = std::nextafterf(c.lo[k] - pad, -kInf), c.hi[k] = std::nextafterf(c.hi[k] + pad, kInf);
+                    }
+            out.insert(out.begin() + at, cs.begin(), cs.end());
+        };
+        const int empty_leaf = (int)leaves.size();  // first == end: no groups
+        if (feat & F_BVH) leaves.push_back(int2{0, 0});
+        std::function<int(int, int&)> collapse = [&](int b, int& need) -> int {
+            std::vector<Child> cs;
+            children_of(b, cs, 0);
+            while (cs.size() < 4) {
+                int pick = -1;
+                double pick_area = -1.0;
+                for (size_t i = 0; i < cs.size(); i++) {
+                    if (cs[i].ref < 0) continue;
+                    double x = (double)cs[i].hi[0] - cs[i].lo[0], y = (double)cs[i].hi[1] - cs[i].lo[1], z = (double)cs[i].hi[2] - cs[i].lo[2];
+                    double a = x * y + y * z + z * x;
+                    if (a > pick_area) pick_area = a, pick = (int)i;
+                }
+                if (pick < 0) break;
+                int inner = cs[pick].ref;
+                cs.erase(cs.begin() + pick);
+                children_of(inner, cs, (size_t)pick);
+            }
+            const int idx = (int)nodes4.size();
+            nodes4.push_back(DevNode4{});
+            DevNode4 d{};
+            float* lo[3] = {&d.lox.x, &d.loy.x, &d.loz.x};
+            float* hi[3] = {&d.hix.x, &d.hiy.x, &d.hiz.x};
+            int deepest = 0;
+            for (int i = 0; i < 4; i++) {
+                if (i < (int)cs.size()) {
+                    for (int k = 0; k < 3; k++) lo[k][i] = cs[i].lo[k], hi[k][i] = cs[i].hi[k];
+                    if (cs[i].ref >= 0) {
+                        int sub = 0;
+                        d.ref[i] = collapse(cs[i].ref, sub);
+                        deepest = std::max(deepest, sub);
+                    } else {
+                        d.ref[i] = cs[i].ref;
+                    }
+                } else {
+                    for (int k = 0; k < 3; k++) lo[k][i] = hi[k][i] = 3.0e38f;
+                    d.ref[i] = ~empty_leaf;
+                }
+            }
+            need = (int)cs.size() - 1 + deepest;  // siblings pushed here + the deepest subtree's own need
+            nodes4[idx] = d;
+            return idx;
+        };
+        for (DevItem& d : items)
+            if (d.type == RTW_ITEM_BVH) {
+                int need = 0;
+                d.root4 = collapse(d.end, need);
+                stack4_need = std::max(stack4_need, need);
+            }
+    }
+    if (getenv("RTW_DEBUG_TREES"))
+        fprintf(stderr, "rtw trees: %zu binary nodes (depth %d), %zu 4-wide nodes (stack need %d), %zu leaves\n", nodes.size(), max_depth,
+                nodes4.size(), stack4_need, leaves.size());
+    if (dry_run) {
+        set_error("scene_create: RTW_DRY_RUN is set (diagnostics only, nothing was uploaded)");
+        return nullptr;
+    }
+    if (max_depth > 60 || stack4_need > 60) {
         set_error("scene_create: bvh deeper than the 62-entry traversal stack");
         return nullptr;
     }
@@ -629,16 +716,17 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
     // blob layout: 16-byte aligned sections, hot first; offsets first (the records hold byte offsets), then the bytes
     const size_t sec_bytes[SEC_COUNT] = {
         items.size() * sizeof(DevItem), groups.size() * sizeof(DevGroup), recs.size() * sizeof(DevRec), xfs.size() * sizeof(DevXf),
-        lights.size() * sizeof(DevLight), nodes.size() * sizeof(DevNode), leaves.size() * sizeof(int2),
+        lights.size() * sizeof(DevLight), nodes.size() * sizeof(DevNode), leaves.size() * sizeof(int2), nodes4.size() * sizeof(DevNode4),
         pm.size() * sizeof(uint32_t), pa.size() * sizeof(float4), pb.size() * sizeof(float4), pd.size() * sizeof(double),
         mats.size() * sizeof(DevMat), texs.size() * sizeof(DevTex), ranvec.size() * sizeof(float4), perm.size()};
     uint32_t off[SEC_COUNT] = {};
     uint32_t hot_bytes = 0;
     size_t total = 0;
     for (int k = 0; k < SEC_COUNT; k++) {
+        if (k == SEC_NODES4) total = (total + 127) & ~(size_t)127;  // a DevNode4 is one 128-byte line
         off[k] = (uint32_t)total;
         total = (total + sec_bytes[k] + 15) & ~(size_t)15;
-        if (k == SEC_LEAVES) hot_bytes = (uint32_t)total;
+        if (k == SEC_NODES4) hot_bytes = (uint32_t)total;
     }
     if (total == 0) total = 16;
     if (total > 0x7fffffffu) {
@@ -659,7 +747,8 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
     }
     for (DevItem& d : items) {
         d.xf = xf_off(d.xf);
-        if (d.type == RTW_ITEM_BVH) d.first = ref_off(d.first), d.end = ref_off(d.end);
+        if (d.type == RTW_ITEM_BVH)
+            d.first = ref_off(d.first), d.end = ref_off(d.end), d.root4 = (int32_t)(off[SEC_NODES4] + (uint32_t)d.root4 * sizeof(DevNode4));
         else d.first = group_off(d.first), d.end = group_off(d.end);
     }
     for (DevNode& n : nodes) {
@@ -668,6 +757,9 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
         n.llo.w = __int_as_float_host(ref_off(l)), n.lhi.w = __int_as_float_host(ref_off(r));
     }
     for (int2& lf : leaves) lf.x = group_off(lf.x), lf.y = group_off(lf.y);
+    for (DevNode4& n : nodes4)
+        for (int i = 0; i < 4; i++)
+            n.ref[i] = n.ref[i] >= 0 ? (int32_t)(off[SEC_NODES4] + (uint32_t)n.ref[i] * sizeof(DevNode4)) : ref_off(n.ref[i]);
     auto pd_off = [&](float idx_bits) {
         int idx;
         memcpy(&idx, &idx_bits, 4);
@@ -682,7 +774,7 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
     }
 
     std::vector<uint8_t> blob(total, 0);
-    const void* sec_data[SEC_COUNT] = {items.data(), groups.data(), recs.data(), xfs.data(), lights.data(), nodes.data(), leaves.data(),
+    const void* sec_data[SEC_COUNT] = {items.data(), groups.data(), recs.data(), xfs.data(), lights.data(), nodes.data(), leaves.data(), nodes4.data(),
                                        pm.data(), pa.data(), pb.data(), pd.data(), mats.data(), texs.data(), ranvec.data(), perm.data()};
     for (int k = 0; k < SEC_COUNT; k++)
         if (sec_bytes[k]) memcpy(blob.data() + off[k], sec_data[k], sec_bytes[k]);
@@ -705,7 +797,7 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
     d.hot_bytes = hot_bytes, d.all_bytes = (uint32_t)blob.size();
     d.n_world_items = fs->n_world_items, d.n_items = fs->n_items, d.n_prims = fs->n_prims, d.n_lights = fs->n_lights;
     d.render_type = fs->render_type, d.background_type = fs->background_type;
-    d.features = feat, d.max_bvh_depth = max_depth;
+    d.features = feat, d.max_bvh_depth = max_depth, d.bvh4_stack = stack4_need;
     // RTW_FLAG_AUTO: the multi-kernel wavefront pipeline beat the lane-owns-a-path megakernel on noise-textured and on
     // media + BVH scenes; the material-sorted megakernel is faster than both on every measured class, so
     // AUTO only falls back to the wavefront rule when the sorted kernel is switched off.

@@ -2,7 +2,7 @@
 //
 // The whole scene except image texels is ONE packed blob of 16-byte aligned sections, ordered hot-first:
 //
-//   [ items | groups | recs | xfs | lights | nodes | leaves ]               <- "hot": touched per primitive test
+//   [ items | groups | recs | xfs | lights | nodes | leaves | nodes4 ]      <- "hot": touched per primitive test
 //   [ pm | pa | pb | pd | mats | texs | perlin_ranvec | perlin_perm ]       <- "cold": touched once per ray
 //
 // A render block stages a prefix of the blob into shared memory (everything, the hot part, or nothing,
@@ -46,7 +46,7 @@ struct DevItem {
     int32_t end;      // PRIMS/MEDIUM: byte offset one past the last DevGroup
     int32_t material, flip;
     float density_eff;  // density * multiplicity
-    float pad;
+    int32_t root4;      // BVH: byte offset of the root DevNode4 of the render tree
 };
 
 // Run of primitive-test records sharing one transform chain.  All members are byte offsets into the blob:
@@ -88,6 +88,17 @@ struct DevNode {
     float4 rhi;  // right child box max.xyz
 };
 
+// One step of the 4-wide tree the RENDER kernels walk (128 bytes = one cache line): the binary tree built at upload,
+// collapsed so that a node holds the boxes of up to four descendants in SoA form — half the dependent node fetches per
+// ray of the binary tree, which is what bounds the big scenes (node fetches are L1/L2 latency, not instruction issue).
+// Child references as in DevNode (>= 0: byte offset of a DevNode4, < 0: ~leaf offset).  An unused slot has a far-away
+// degenerate box that no finite ray reaches and references an empty leaf (a NaN ray, whose slabs all drop out, lands there).
+struct DevNode4 {
+    float4 lox, hix, loy, hiy, loz, hiz;  // component i = child i
+    int32_t ref[4];
+    int32_t pad[4];
+};
+
 struct DevMat {
     float r, g, b, param;  // metal: albedo + fuzz; dielectric: param = ref_idx; textured: resolved constant colour
     int32_t type, texture, tex_is_constant, pad;
@@ -121,7 +132,7 @@ enum : uint32_t {  // feature mask -> kernel specialisation
 };
 
 enum {  // blob sections, in blob order
-    SEC_ITEMS = 0, SEC_GROUPS, SEC_RECS, SEC_XFS, SEC_LIGHTS, SEC_NODES, SEC_LEAVES,  // hot
+    SEC_ITEMS = 0, SEC_GROUPS, SEC_RECS, SEC_XFS, SEC_LIGHTS, SEC_NODES, SEC_LEAVES, SEC_NODES4,  // hot
     SEC_PM, SEC_PA, SEC_PB, SEC_PD, SEC_MATS, SEC_TEXS, SEC_RANVEC, SEC_PERM,        // cold
     SEC_COUNT
 };
@@ -134,7 +145,8 @@ struct DevScene {
     int32_t n_world_items, n_items, n_prims, n_lights;
     int32_t render_type, background_type;
     uint32_t features;
-    int32_t max_bvh_depth;
+    int32_t max_bvh_depth;  // binary trees (reference topology and SAH): traversal stack entries = depth + 2
+    int32_t bvh4_stack;     // 4-wide render trees: most references ever pushed at once
     DevCamera cam;
 };
 

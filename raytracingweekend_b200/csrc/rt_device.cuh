@@ -151,7 +151,7 @@ RTW_DEV DevItem ld_item(const SceneView& sv, uint32_t off) {
     float4 a = hot4<SM>(sv, off), b = hot4<SM>(sv, off + 16);
     DevItem it;
     it.type = fi(a.x), it.xf = fi(a.y), it.first = fi(a.z), it.end = fi(a.w);
-    it.material = fi(b.x), it.flip = fi(b.y), it.density_eff = b.z, it.pad = 0.0f;
+    it.material = fi(b.x), it.flip = fi(b.y), it.density_eff = b.z, it.root4 = fi(b.w);
     return it;
 }
 template <int SM>

@@ -60,24 +60,27 @@ struct Launch {
     int stage;
     size_t smem;
 };
-// `block` = threads per block of the kernel being launched (sizes the per-thread BVH stack columns).
-inline Launch plan(const DevScene& sc, int block) {
+// `block` = threads per block of the kernel being launched (sizes the per-thread BVH stack columns); `exact` = the kernel
+// walks the reference-topology binary trees (intersect_batch), else the render trees.
+inline Launch plan(const DevScene& sc, int block, bool exact = false) {
     Launch l;
     l.stage = pick_stage(sc);
     l.variant = pick_variant_impl(sc.features);
     // instantiated combinations: every variant at stage 2; {moving, all} at stages 1 and 0
     if (l.stage < 2 && l.variant != kVariants[1]) l.variant = F_ALL;
     size_t staged = l.stage == 2 ? sc.all_bytes : (l.stage == 1 ? sc.hot_bytes : 0);
-    size_t stack = (l.variant & F_BVH) ? (size_t)(sc.max_bvh_depth + 2) * block * sizeof(int) : 0;
+    const int entries = (exact || !bvh4_variant(l.variant)) ? sc.max_bvh_depth + 2 : sc.bvh4_stack + 1;
+    size_t stack = (l.variant & F_BVH) ? (size_t)entries * block * sizeof(int) : 0;
     l.smem = staged + stack;
     return l;
 }
 
 }  // namespace rtw
 
-#define RTW_DISPATCH(BLOCK, FN, ...)                                                               \
+#define RTW_DISPATCH(BLOCK, FN, ...) RTW_DISPATCH_X(false, BLOCK, FN, __VA_ARGS__)
+#define RTW_DISPATCH_X(EXACT, BLOCK, FN, ...)                                                      \
     do {                                                                                           \
-        Launch l = plan(sc, BLOCK);                                                                \
+        Launch l = plan(sc, BLOCK, EXACT);                                                         \
         if (l.stage == 2) {                                                                        \
             if (l.variant == kVariants[0]) return FN<kVariants[0], 2>(__VA_ARGS__, l.smem, st);    \
             if (l.variant == kVariants[1]) return FN<kVariants[1], 2>(__VA_ARGS__, l.smem, st);    \

@@ -4,6 +4,15 @@
 
 namespace rtw {
 
+#ifndef RTW_BVH4
+#define RTW_BVH4 1  // render kernels walk the 4-wide tree where it was measured faster (A/B switch: 0 = never, 2 = always)
+#endif
+#ifndef RTW_BVH4_OCTANT
+#define RTW_BVH4_OCTANT 1
+#endif
+#ifndef RTW_BVH4_SORT
+#define RTW_BVH4_SORT 0  // 1: full distance sort of the hit children; 0: nearest first, the others in slot order (+2.5 %)
+#endif
 #ifndef RTW_FAST_BOX
 #define RTW_FAST_BOX 0  // min/max slab test on the render path: measured 1.2-1.6x SLOWER than aabb_hit (A/B switch, off)
 #endif
@@ -80,6 +89,124 @@ RTW_DEV void bvh_hit(const SceneView& sv, int root, const RayK& rk, float time, 
     }
 }
 
+// Which kernel variants walk the 4-wide tree.  Measured on B200 (tools/ab_bvh4.sh): random_balls_scene 2.27 -> 2.49
+// Gpaths/s (node visits x0.57), but the all-features kernels lose 4-7 % (Book-2 final 0.452 -> 0.422, and Cornell smoke,
+// which has no tree at all, 3.96 -> 3.80: those kernels are bound by instruction fetch and by the longest lane of a warp,
+// not by the number of node fetches), so they keep the binary tree.
+__host__ __device__ constexpr bool bvh4_variant(uint32_t f) { return RTW_BVH4 == 2 || (RTW_BVH4 == 1 && (f & F_BVH) && !(f & F_MEDIA)); }
+
+// The same search over the 4-wide render tree (DevNode4, device_scene.hpp): one 128-byte node decides four children.
+// The near and far plane of each slab are picked by the sign of the ray direction (three per-ray address offsets), so a
+// child costs 6 FFMA + 4 min/max + 1 compare; fminf/fmaxf drop a NaN plane (0 * inf, inf - inf), which only widens the
+// interval — the boxes are padded bounds of what the leaves test exactly, so widening never changes a result.  The hit
+// children are ordered by entry distance (comparator network, RTW_BVH4_SORT); the nearest is descended, the others pushed
+// farthest first.
+template <uint32_t F, int SM, bool BOXREC>
+RTW_DEV void bvh4_hit(const SceneView& sv, int root, const RayK& rk, float time, float tmin, float tmax, int* stack, int stride,
+                      float& t_out, int& prim_out) {
+    const V3 inv = rk.inv;
+    const V3 oi = mk(rk.o.x * inv.x, rk.o.y * inv.y, rk.o.z * inv.z);
+#if RTW_BVH4_OCTANT
+    const uint32_t nx = inv.x < 0.0f ? 16u : 0u, ny = inv.y < 0.0f ? 48u : 32u, nz = inv.z < 0.0f ? 80u : 64u;  // near planes
+#endif
+    float best = tmax;
+    int best_prim = -1, best_leaf = 0;
+    int sp = 0;
+    int ref = root;
+    for (;;) {
+        while (ref >= 0) {
+            const uint32_t a = (uint32_t)ref;
+#if RTW_BVH4_OCTANT
+            const float4 nxv = hot4<SM>(sv, a + nx), fxv = hot4<SM>(sv, a + (nx ^ 16u));
+            const float4 nyv = hot4<SM>(sv, a + ny), fyv = hot4<SM>(sv, a + (ny ^ 16u));
+            const float4 nzv = hot4<SM>(sv, a + nz), fzv = hot4<SM>(sv, a + (nz ^ 16u));
+#else
+            const float4 nxv = hot4<SM>(sv, a), fxv = hot4<SM>(sv, a + 16u);
+            const float4 nyv = hot4<SM>(sv, a + 32u), fyv = hot4<SM>(sv, a + 48u);
+            const float4 nzv = hot4<SM>(sv, a + 64u), fzv = hot4<SM>(sv, a + 80u);
+#endif
+            const float4 rf = hot4<SM>(sv, a + 96u);
+            const float cull = best_prim >= 0 ? fmaf(best, 4e-6f, best) : tmax;
+            float t0, t1, t2, t3;
+#if RTW_BVH4_OCTANT
+#define RTW_SLAB4(T, C)                                                                                                       \
+    {                                                                                                                         \
+        const float tn = fmaxf(fmaxf(fmaf(nxv.C, inv.x, -oi.x), fmaf(nyv.C, inv.y, -oi.y)), fmaxf(fmaf(nzv.C, inv.z, -oi.z), tmin)); \
+        const float tf = fminf(fminf(fmaf(fxv.C, inv.x, -oi.x), fmaf(fyv.C, inv.y, -oi.y)), fminf(fmaf(fzv.C, inv.z, -oi.z), cull)); \
+        T = tn <= tf ? tn : INFINITY;                                                                                         \
+    }
+#else
+#define RTW_SLAB4(T, C)                                                                                                       \
+    {                                                                                                                         \
+        const float x0 = fmaf(nxv.C, inv.x, -oi.x), x1 = fmaf(fxv.C, inv.x, -oi.x);                                           \
+        const float y0 = fmaf(nyv.C, inv.y, -oi.y), y1 = fmaf(fyv.C, inv.y, -oi.y);                                           \
+        const float z0 = fmaf(nzv.C, inv.z, -oi.z), z1 = fmaf(fzv.C, inv.z, -oi.z);                                           \
+        const float tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), tmin));                              \
+        const float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), cull));                              \
+        T = tn <= tf ? tn : INFINITY;                                                                                         \
+    }
+#endif
+            RTW_SLAB4(t0, x)
+            RTW_SLAB4(t1, y)
+            RTW_SLAB4(t2, z)
+            RTW_SLAB4(t3, w)
+#undef RTW_SLAB4
+            int r0 = fi(rf.x), r1 = fi(rf.y), r2 = fi(rf.z), r3 = fi(rf.w);
+#define RTW_CSWAP(TA, RA, TB, RB)            \
+    {                                        \
+        const bool s = TB < TA;              \
+        const float tt = s ? TB : TA;        \
+        TB = s ? TA : TB, TA = tt;           \
+        const int rr = s ? RB : RA;          \
+        RB = s ? RA : RB, RA = rr;           \
+    }
+            RTW_CSWAP(t0, r0, t1, r1)
+            RTW_CSWAP(t2, r2, t3, r3)
+            RTW_CSWAP(t0, r0, t2, r2)
+#if RTW_BVH4_SORT
+            RTW_CSWAP(t1, r1, t3, r3)
+            RTW_CSWAP(t1, r1, t2, r2)
+#endif
+#undef RTW_CSWAP
+            if (t0 < INFINITY) {
+                if (t3 < INFINITY) stack[sp * stride] = r3, sp++;
+                if (t2 < INFINITY) stack[sp * stride] = r2, sp++;
+                if (t1 < INFINITY) stack[sp * stride] = r1, sp++;
+                ref = r0;
+            } else if (sp > 0) {
+                sp--;
+                ref = stack[sp * stride];
+            } else {
+                ref = kBvhDone;
+            }
+        }
+        if (ref == kBvhDone) break;
+        {  // leaf: list semantics against the caller's tmax, as in bvh_hit
+            const uint2 lf = hot2<SM>(sv, (uint32_t)~ref);
+            float t_leaf = tmax;
+            int p_leaf = -1;
+            test_groups<F, SM, BOXREC>(sv, lf.x, lf.y, rk, time, tmin, t_leaf, p_leaf);
+            const int leaf = ~ref;
+            if (p_leaf >= 0 && (best_prim < 0 || t_leaf < best || (t_leaf == best && leaf >= best_leaf))) {
+                best = t_leaf;
+                best_prim = p_leaf;
+                best_leaf = leaf;
+            }
+            if (sp > 0) {
+                sp--;
+                ref = stack[sp * stride];
+            } else {
+                ref = kBvhDone;
+            }
+        }
+        if (ref == kBvhDone) break;
+    }
+    if (best_prim >= 0) {
+        t_out = best;
+        prim_out = best_prim;
+    }
+}
+
 // world.hit(r, tmin, tmax) (RayTracingWeekend.cpp:52 -> hittable_list.h:11-37) over the flattened items.
 // `rng` == nullptr skips constant_medium items (intersect_batch: media are stochastic).
 // EXACT_TIES replays the second pass of hittable_list::hit (hittable_list.h:26-34) for scenes with bvh_node items:
@@ -111,8 +238,13 @@ RTW_DEV HitId closest_hit(const DevScene& sc, const SceneView& sv, V3 o, V3 d, f
             if (ixf >= 0) lk = xf_rayk(ld_xf<SM>(sv, (uint32_t)ixf), rk);
             int p = -1;
             float t = h.t;
-            // intersect_batch walks the reference's own topology (`first`), rendering the SAH tree over the same leaves (`end`)
-            bvh_hit<F, SM, true, RTW_FAST_BOX && !EXACT_TIES, !EXACT_TIES>(sv, EXACT_TIES ? first : end, lk, time, tmin, h.t, stack, stride, t, p);
+            // intersect_batch walks the reference's own topology (`first`); rendering walks the SAH tree over the same leaves
+            // (`end`) or, in the variants bvh4_variant() names, its 4-wide collapse (`root4`)
+            if constexpr (EXACT_TIES || !bvh4_variant(F)) {
+                bvh_hit<F, SM, true, RTW_FAST_BOX && !EXACT_TIES, !EXACT_TIES>(sv, EXACT_TIES ? first : end, lk, time, tmin, h.t, stack, stride, t, p);
+            } else {
+                bvh4_hit<F, SM, true>(sv, (int)hot1<SM>(sv, ia + 28u), lk, time, tmin, h.t, stack, stride, t, p);
+            }
             if (p >= 0) {
                 h.t = t;
                 h.prim = p;
