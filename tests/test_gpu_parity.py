@@ -173,6 +173,50 @@ def test_spp_shards_are_disjoint_streams_and_sum_exactly(scenes):
     assert np.all(acc[..., 3] == 32) and np.allclose(acc[..., :3], full[..., :3], rtol=1e-5, atol=1e-5)
 
 
+def test_full_size_cfg4_properties(scenes):
+    """BASELINE.json configs[3] at its FULL size (Cornell box + glass sphere + aluminium box, 1024x1024, 1024 spp = 1.07 G
+    paths), through size-independent properties:
+      * the launch is bit-reproducible (64-bit fixed-point pixel sums), so its checksum is too;
+      * eight spp shards (the 8-GPU partition of SURVEY 8e, run back to back on one GPU) trace exactly the rays of the
+        unsharded render and their sum equals it up to FP32 reassociation of the partial sums;
+      * rays per path equals the FP64 oracle's figure for this scene (5.118, tools/count_flops.py) to 0.5 %;
+      * box-filtered down to 64x64 it is the image of the unmodified reference's serial CPU render (golden fixture,
+        4096 spp): per-pixel z-test with the reference's own sample variance, and channel means to 1 %."""
+    b, sc = scenes("cornell_box_aluminum", 1.0)
+    nx = ny = 1024
+    spp = 1024
+    full, st = sc.render(nx, ny, spp, seed=11)
+    again, st2 = sc.render(nx, ny, spp, seed=11)
+    assert np.array_equal(full, again) and st["rays"] == st2["rays"]
+    assert st["paths"] == nx * ny * spp and np.all(full[..., 3] == spp)
+    G = 8
+    acc = np.zeros((ny, nx, 4), np.float64)
+    rays = 0
+    for g in range(G):
+        part, stp = sc.render(nx, ny, spp // G, spp_begin=g * (spp // G), seed=11)
+        acc += part
+        rays += stp["rays"]
+    assert rays == st["rays"]
+    assert np.all(acc[..., 3] == spp)
+    fin = np.isfinite(full[..., :3]).all(axis=2)
+    assert fin.mean() > 0.9999 and np.array_equal(fin, np.isfinite(acc[..., :3]).all(axis=2))
+    assert np.allclose(acc[..., :3][fin], full[..., :3][fin], rtol=2e-5, atol=1e-3)
+    assert abs(st["rays"] / st["paths"] - 5.118) < 0.005 * 5.118
+
+    g = np.load(os.path.join(GOLDEN, "image_cornell_box_aluminum.npz"))
+    rn, rspp = int(g["nx"]), int(g["spp"])
+    f = nx // rn
+    img = np.where(fin[..., None], full[..., :3].astype(np.float64), 0.0) / spp
+    gm = img.reshape(rn, f, rn, f, 3).mean(axis=(1, 3))
+    rm = g["sum"] / rspp
+    rvar = np.maximum(g["sumsq"] / rspp - rm * rm, 0.0) / rspp
+    ok = np.isfinite(rm).all(axis=2)
+    # the GPU side averages 256 x 1024 samples per reference pixel: its variance is ~1/64 of the reference's
+    z = (np.abs(gm - rm) / np.sqrt(rvar * (1.0 + 1.0 / 64.0) + 1e-12))[ok]
+    assert (z > 4).mean() < 0.005 and np.median(z) < 1.0, ((z > 4).mean(), np.median(z))
+    assert np.allclose(gm[ok].mean(axis=0), rm[ok].mean(axis=0), rtol=0.02)
+
+
 def test_render_shapes_flags_and_depth(scenes):
     b, sc = scenes("cornell_box_aluminum", 1.0)
     # ragged image (not a multiple of the 16x8 block tile), spp = 1
