@@ -34,13 +34,21 @@ SPP = 1024
 MAX_DEPTH = 100
 # SURVEY §8d / DESIGN.md §5: algorithmic FP32 flops per path of the reference's math on this scene, counted by the
 # instrumented oracle (tools/count_flops.py: oracle_events_*, 64x64x64 spp sample, Appendix D cost table).
-NCU_DRAM_BYTES_PER_LAUNCH = 117504 + 236032  # read + write, see roofline.traffic below
+NCU_DRAM_BYTES_PER_LAUNCH = 70400 + 160512  # read + write, see roofline.traffic below
 FLOP_PER_PATH = 1344.5
 FP32_PEAK_SPEC_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12  # 74.4
 
 
+CONFIGS = {  # --config: the headline workload (default) and the scaling-sweep shape of BASELINE.json configs[4]
+    # nx, ny, spp, note, algorithmic flop/path (tools/count_flops.py; the 16:9 frame sees past the box: 3.31 rays/path, not 5.11)
+    "cfg4": (1024, 1024, 1024, "BASELINE.json configs[3]", 1344.5),
+    "cfg5": (3840, 2160, 4096, "BASELINE.json configs[4], spp-sharded scaling sweep", 819.3),
+}
+CONFIG_NOTE = CONFIGS["cfg4"][3]
+
+
 def workload_config(n_gpus: int) -> dict:
-    return {"workload": f"{SCENE} (Book-3 Cornell box, glass sphere + aluminium box; BASELINE.json configs[3])",
+    return {"workload": f"{SCENE} (Book-3 Cornell box, glass sphere + aluminium box; {CONFIG_NOTE})",
             "nx": NX, "ny": NY, "spp": SPP, "max_depth": MAX_DEPTH, "paths_per_step": NX * NY * SPP,
             "parallelism": f"spp-shard x{n_gpus} + ncclReduce" if n_gpus > 1 else "single GPU",
             "l2": "flushed between timed steps (256 MiB write); scene data is ~1 KB and cache-resident by design",
@@ -97,7 +105,7 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------------ CPU reference
 def cpu_reference(target_seconds: float = 15.0) -> dict:
     """The reference's own image loop + color() (oracle/_ref/ref_harness: unmodified sources, std::thread ppl shim)
-    on all host cores, on a bounded sample of the SAME workload: same scene, same 1024x1024 resolution, reduced spp
+    on all host cores, on a bounded sample of the SAME workload: same scene, same resolution (1024x1024), reduced spp
     (paths/s does not depend on spp).  Falls back to the oracle port when the reference binary is absent."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import oracle_lib as ol
@@ -145,7 +153,7 @@ def run_reference(args) -> None:
             "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_config(args.gpus),
             "cpu_baseline": {"value": v, "unit": "paths/s", "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": v, "unit": "paths/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "note": "ms_per_step is extrapolated to the full 1024-spp step from the bounded sample"}
+            "note": f"ms_per_step is extrapolated to the full {SPP}-spp step from the bounded sample"}
     print(json.dumps(line))
 
 
@@ -282,11 +290,12 @@ def run_ours(args) -> None:
     sorted_kernel = os.environ.get("RTW_MEGA_SORTED", "1") != "0"
     roofline = {"bound": "fp32-issue", "achieved": achieved, "peak": peak.value, "unit": "TFLOP/s",
                 "frac": achieved / peak.value if peak.value else None,
-                # dram__bytes_read.sum + dram__bytes_write.sum of ONE full-size (1024 spp, whole image) launch, from the ncu
-                # --set full capture summarised in profiles/r1_sorted_cornell_ncu_details.txt; the 16 MB image was still
+                # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch over the whole 1024x1024 image (256 spp; the traffic
+                # is the scene read and the image store and does not grow with spp), from the ncu
+                # --set full capture summarised in profiles/r1_sorted_v6_cornell_ncu_details.txt; the 16 MB image was still
                 # in L2 when the kernel ended.  Only valid for the single-GPU shape of that capture.
-                "traffic": NCU_DRAM_BYTES_PER_LAUNCH if world == 1 and sorted_kernel else None,
-                "traffic_unit": "bytes per launch (ncu, profiles/r1_sorted_cornell_ncu_details.txt)",
+                "traffic": NCU_DRAM_BYTES_PER_LAUNCH if world == 1 and sorted_kernel and (NX, NY) == (1024, 1024) else None,
+                "traffic_unit": "bytes per launch (ncu, profiles/r1_sorted_v6_cornell_ncu_details.txt)",
                 "peak_source": "FFMA micro-benchmark run in this process (rtw_measure_fp32_peak); spec-derived "
                                f"{FP32_PEAK_SPEC_TFLOPS:.1f} TFLOP/s at 1965 MHz",
                 "frac_of_spec": achieved / FP32_PEAK_SPEC_TFLOPS,
@@ -317,7 +326,11 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="cfg4", choices=sorted(CONFIGS),
+                    help="cfg4 = the headline workload (default); cfg5 = Cornell 3840x2160x4096, the scaling-sweep shape")
     args = ap.parse_args()
+    global NX, NY, SPP, CONFIG_NOTE, FLOP_PER_PATH
+    NX, NY, SPP, CONFIG_NOTE, FLOP_PER_PATH = CONFIGS[args.config]
     if args.impl == "reference":
         run_reference(args)
     else:

@@ -187,15 +187,20 @@ def test_full_size_cfg4_properties(scenes):
     spp = 1024
     full, st = sc.render(nx, ny, spp, seed=11)
     again, st2 = sc.render(nx, ny, spp, seed=11)
-    assert np.array_equal(full, again) and st["rays"] == st2["rays"]
+    assert np.array_equal(full, again, equal_nan=True) and st["rays"] == st2["rays"]  # NaN pixels stay NaN (Q21)
     assert st["paths"] == nx * ny * spp and np.all(full[..., 3] == spp)
     G = 8
     acc = np.zeros((ny, nx, 4), np.float64)
     rays = 0
+    rn = 64  # the golden fixture's resolution
+    f = nx // rn
+    shard_means = []
     for g in range(G):
         part, stp = sc.render(nx, ny, spp // G, spp_begin=g * (spp // G), seed=11)
         acc += part
         rays += stp["rays"]
+        p3 = np.nan_to_num(part[..., :3].astype(np.float64), nan=0.0, posinf=0.0, neginf=0.0) / (spp // G)
+        shard_means.append(p3.reshape(rn, f, rn, f, 3).mean(axis=(1, 3)))
     assert rays == st["rays"]
     assert np.all(acc[..., 3] == spp)
     fin = np.isfinite(full[..., :3]).all(axis=2)
@@ -204,15 +209,20 @@ def test_full_size_cfg4_properties(scenes):
     assert abs(st["rays"] / st["paths"] - 5.118) < 0.005 * 5.118
 
     g = np.load(os.path.join(GOLDEN, "image_cornell_box_aluminum.npz"))
-    rn, rspp = int(g["nx"]), int(g["spp"])
-    f = nx // rn
+    assert int(g["nx"]) == rn and int(g["ny"]) == rn
+    rspp = int(g["spp"])
     img = np.where(fin[..., None], full[..., :3].astype(np.float64), 0.0) / spp
     gm = img.reshape(rn, f, rn, f, 3).mean(axis=(1, 3))
     rm = g["sum"] / rspp
     rvar = np.maximum(g["sumsq"] / rspp - rm * rm, 0.0) / rspp
     ok = np.isfinite(rm).all(axis=2)
-    # the GPU side averages 256 x 1024 samples per reference pixel: its variance is ~1/64 of the reference's
-    z = (np.abs(gm - rm) / np.sqrt(rvar * (1.0 + 1.0 / 64.0) + 1e-12))[ok]
+    # variance of the reference's pixel mean: its own sample variance is heavy-tailed (a pixel whose 4096 samples missed
+    # every firefly under-reports it), so it is floored by the spread of the eight GPU shards (f*f*spp/G samples each),
+    # rescaled to 4096 samples; the GPU mean itself has f*f*spp samples per reference pixel
+    n_shard = f * f * (spp // G)
+    var_shard = np.var(np.stack(shard_means), axis=0, ddof=1)
+    sigma2 = np.maximum(rvar, var_shard * n_shard / rspp) + var_shard / G
+    z = (np.abs(gm - rm) / np.sqrt(sigma2 + 1e-12))[ok]
     assert (z > 4).mean() < 0.005 and np.median(z) < 1.0, ((z > 4).mean(), np.median(z))
     assert np.allclose(gm[ok].mean(axis=0), rm[ok].mean(axis=0), rtol=0.02)
 
