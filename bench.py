@@ -175,6 +175,8 @@ def run_ours(args) -> None:
             raise SystemExit("launch with torchrun --nproc-per-node N for --gpus N")
     torch.cuda.set_device(local)
     if world > 1:
+        # NCCL prints its version banner (NCCL_DEBUG=VERSION/INFO on the box) to stdout by default: keep stdout = ONE JSON line
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     lib = _lib.load()  # fails loudly when the CUDA library is missing
 

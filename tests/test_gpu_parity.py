@@ -119,6 +119,47 @@ def test_render_path_by_path_vs_oracle_philox(scenes, scene, nx, ny, spp):
     assert np.allclose(g.mean(axis=(0, 1)), osum.mean(axis=(0, 1)), rtol=0.05, atol=1e-3 * spp)
 
 
+@pytest.mark.parametrize("name", ["kitchen_sink", "every_light_type", "small_trees", "empty_world"])
+def test_composed_scenes_path_by_path_vs_oracle(name):
+    """Scenes composed through the builder API (tests/custom_scenes.py) that combine what the named scenes do not: nested
+    translate/rotate_y chains, a flipped rotated rect, a hollow glass sphere, a medium in a rotated box, bvh_node with
+    1, 2, 3 and 16 objects (one tree under a transform), every light type incl. the base-class defaults, no lights, an
+    empty world.  Same check as above: FP32 kernel vs FP64 oracle on the same Philox streams."""
+    from custom_scenes import CUSTOM
+
+    nx, ny, spp = 48, 32, 8
+    b = CUSTOM[name](nx / ny)
+    sc = rtw.Scene(b)
+    for flags in (0, rtw._lib.RTW_FLAG_WAVEFRONT):
+        acc, st = sc.render(nx, ny, spp, seed=3, flags=flags)
+        osum, _, orays = ol.oracle_render(b, nx, ny, spp, mode="philox", seed=3)
+        g = acc[..., :3].astype(np.float64)
+        assert np.all(acc[..., 3] == spp)
+        close = np.isclose(g, osum, rtol=2e-3, atol=1e-3 * spp).all(axis=2)
+        assert close.mean() >= (1.0 if name == "empty_world" else 0.93), f"{name}: {close.mean():.4f} of pixels path-exact"
+        assert abs(st["rays"] - orays) / orays < 0.02
+        assert np.allclose(g.mean(axis=(0, 1)), osum.mean(axis=(0, 1)), rtol=0.05, atol=1e-3 * spp)
+    # world.hit() on the camera's primary rays: ids and t against the oracle
+    cam = b.flatten().contents.camera
+    o, llc = np.array(cam.origin), np.array(cam.lower_left_corner)
+    h, v = np.array(cam.horizontal), np.array(cam.vertical)
+    s, t = np.meshgrid((np.arange(64) + 0.37) / 64, (np.arange(48) + 0.61) / 48)
+    d = llc + s.reshape(-1, 1) * h + t.reshape(-1, 1) * v - o
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    rays = np.concatenate([np.tile(o, (len(d), 1)), d, np.full((len(d), 1), 0.5)], axis=1).astype(np.float32)
+    gpu = sc.intersect_batch(rays)
+    ref = ol.oracle_hits(b, rays.astype(np.float64))
+    hit = ref[:, 0] == 1
+    flips = np.mean((gpu["prim"] >= 0) != hit)
+    assert flips <= 2e-3, flips
+    both = hit & (gpu["prim"] >= 0)
+    same = gpu["prim"][both] == ref[both, 11].astype(np.int32)
+    assert same.mean() >= 0.998
+    rel = np.abs(gpu["t"][both][same] - ref[both, 1][same]) / np.abs(ref[both, 1][same])
+    assert rel.max() < T_REL_TOL if rel.size else True
+    sc.close()
+
+
 @pytest.mark.parametrize("scene", SCENES)
 def test_converged_image_vs_reference_render(scenes, scene):
     """Tier 3: GPU render vs the unmodified reference's serial CPU render (different RNG streams by construction).
