@@ -302,6 +302,10 @@ def run_ours(args) -> None:
                                f"{FP32_PEAK_SPEC_TFLOPS:.1f} TFLOP/s at 1965 MHz",
                 "frac_of_spec": achieved / FP32_PEAK_SPEC_TFLOPS,
                 "algorithmic_flop_per_path": fpp,
+                # the roofline this kernel actually sits under is warp-instruction ISSUE (one per scheduler per cycle, every
+                # opcode): ncu sm__inst_issued / issue slots of the cfg4 capture (profiles/r1_sorted_v6_cornell_ncu_details.txt);
+                # the algorithmic count above excludes compares, selects, address/loop arithmetic and the Philox integer rounds
+                "issue_slots_busy_ncu": 0.785 if sorted_kernel and (NX, NY) == (1024, 1024) else None,
                 "kernel": "render_sorted (material-sorted megakernel, csrc/sorted.cu)" if sorted_kernel else "render_megakernel",
                 "kernel_ms_per_launch": kern_ms / args.steps,
                 "hbm": {"algorithmic_bytes_per_launch": NX * NY * 16, "achieved_gbs": NX * NY * 16 / (kern_ms / args.steps * 1e-3) / 1e9,
