@@ -14,6 +14,13 @@
 //            lanes) -> classify -> store state -> push.  Terminal units add their radiance and start 32 new camera
 //            rays on the spot, so camera maths also runs at full lanes.
 //
+// Ring capacity = number of slots is enough only because a consumer reads (and clears) its entries right after the CAS
+// that claimed them: entries that are claimed but not yet read still occupy ring positions behind the head, and while they
+// do the tail may run at most `capacity - 32` ahead of the head.  A warp that kept claimed entries unread across a whole
+// unit (e.g. claiming 64 and running two units) lets other warps cycle the head forward until producers wrap onto them —
+// lost slots, `live` never reaches 0, the block never ends (measured: that variant hung).  Do not batch claims without
+// doubling the rings.
+//
 // Per-pixel sums are 64-bit fixed point (2^-24) in shared memory: integer adds commute, so the image stays
 // bit-reproducible although units run in a timing-dependent order.  Samples that are not finite or >= 8192 go to a
 // float side accumulator (NaN / Inf propagate like in the reference).  HBM traffic is unchanged: one 16-byte
