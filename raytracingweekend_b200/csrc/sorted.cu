@@ -58,7 +58,7 @@ struct SortedCtl {
 };
 
 constexpr size_t sorted_pool_bytes(int pt) {
-    return (size_t)pool_slots(pt) * 64 + (size_t)C_QUEUES * queue_cap(pt) * 2 + (size_t)kSPix * 3 * (8 + 4) + sizeof(SortedCtl) + 64;
+    return (size_t)pool_slots(pt) * 64 + (size_t)C_QUEUES * queue_cap(pt) * 2 + (size_t)kSPix * (3 * (8 + 4) + 4) + sizeof(SortedCtl) + 64;
 }
 
 template <uint32_t F, int SM, int PT, int MB>
@@ -79,7 +79,8 @@ __global__ void __launch_bounds__(kSBlock, MB) render_sorted(const __grid_consta
     uint4* stD = reinterpret_cast<uint4*>(stC + kSPool);  // item, global pixel index, sample, bounce | pixel slot << 16
     unsigned long long* fx = reinterpret_cast<unsigned long long*>(stD + kSPool);  // [3][kSPix] fixed-point sums
     float* fl = reinterpret_cast<float*>(fx + 3 * kSPix);                           // [3][kSPix] side sums
-    volatile uint16_t* queue = reinterpret_cast<volatile uint16_t*>(fl + 3 * kSPix);  // [C_QUEUES][kQCap]
+    unsigned int* prays = reinterpret_cast<unsigned int*>(fl + 3 * kSPix);          // [kSPix] color() invocations per pixel
+    volatile uint16_t* queue = reinterpret_cast<volatile uint16_t*>(prays + kSPix);  // [C_QUEUES][kQCap]
     SortedCtl* ctl = reinterpret_cast<SortedCtl*>(const_cast<uint16_t*>(queue) + C_QUEUES * kQCap);
     volatile unsigned int* vhead = ctl->head;
     volatile unsigned int* vtail = ctl->tail;
@@ -104,6 +105,7 @@ __global__ void __launch_bounds__(kSBlock, MB) render_sorted(const __grid_consta
     };
 
     for (int k = tid; k < 3 * kSPix; k += kSBlock) fx[k] = 0ull, fl[k] = 0.0f;
+    for (int k = tid; k < kSPix; k += kSBlock) prays[k] = 0u;
     for (int k = tid; k < C_QUEUES * kQCap; k += kSBlock) queue[k] = kQEmpty;
     __syncthreads();
     for (int s = tid; s < kSPool; s += kSBlock) queue[C_REGEN * kQCap + s] = (uint16_t)s;  // every slot needs a camera ray
@@ -113,7 +115,6 @@ __global__ void __launch_bounds__(kSBlock, MB) render_sorted(const __grid_consta
 
     Rng rng;
     rng.rk = rp.rk;
-    unsigned long long rays = 0;
     const int pref = (tid >> 5) % C_TERM;  // the class this warp looks at first: one of the four scatter classes
     for (;;) {
         // ---- claim a unit: 32 entries of a class that has them (each warp starts looking at a different class, which
@@ -186,6 +187,9 @@ __global__ void __launch_bounds__(kSBlock, MB) render_sorted(const __grid_consta
                 alive = shade_hit<F, SM>(sc, sv, rng, bounce, hit, ray, beta, L, c == C_LAMB || c == C_DIEL);
                 if (alive && (int)bounce >= rp.max_depth) alive = false;  // :47-48: the next color() returns 0
                 if (!alive) {                                             // :235-239
+                    // the path's color() invocations = its last bounce index; counted per pixel at the path's end (a per-lane
+                    // counter live across the whole loop was the one value this kernel spilled to local memory)
+                    atomicAdd(prays + pix, bounce);
                     const float v[3] = {L.x, L.y, L.z};
 #pragma unroll
                     for (int ch = 0; ch < 3; ch++) {
@@ -223,18 +227,19 @@ __global__ void __launch_bounds__(kSBlock, MB) render_sorted(const __grid_consta
         int ncls = (c >= C_TERM) ? C_DEAD : C_REGEN;  // a terminal/regen lane only stays dead when the pool is empty
         if (alive) {
             bounce++;
-            rays++;
             const HitId hit = closest_hit<F, SM, false>(sc, sv, ray.o, ray.d, ray.time, 0.001f, FLT_MAX, &rng, bounce, stack, kSBlock);
             ncls = C_TERM;
             if (hit.prim != -1 && sc.render_type != RTW_RENDER_NORMAL) {
                 uint32_t pm;
                 const int mat_idx = hit_material<SM>(sc, sv, hit, pm);
                 const int mt = ld_mat<SM>(sv, sc.off[SEC_MATS] + (uint32_t)mat_idx * 32u).type;
-                ncls = mt == RTW_MAT_DIFFUSE_LIGHT ? C_TERM
-                       : mt == RTW_MAT_METAL       ? C_METAL
-                       : mt == RTW_MAT_DIELECTRIC  ? C_DIEL
-                       : mt == RTW_MAT_ISOTROPIC   ? C_ISO
-                                                   : C_LAMB;
+                // class of material type `mt` from a packed table (one shift instead of a jump table with four divergent
+                // arms): nibble mt of kClassOfMat; any other value shades as lambertian, like the switch in shade_hit
+                constexpr uint32_t kClassOfMat = (uint32_t)C_LAMB << (4 * RTW_MAT_LAMBERTIAN) | (uint32_t)C_METAL << (4 * RTW_MAT_METAL) |
+                                                 (uint32_t)C_DIEL << (4 * RTW_MAT_DIELECTRIC) | (uint32_t)C_TERM << (4 * RTW_MAT_DIFFUSE_LIGHT) |
+                                                 (uint32_t)C_ISO << (4 * RTW_MAT_ISOTROPIC);
+                static_assert(C_LAMB == 0, "nibbles of unknown material types must read as lambertian");
+                ncls = (int)((kClassOfMat >> (min((uint32_t)mt, 7u) * 4u)) & 7u);
             }
             stA[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, hit.t);
             stB[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, ray.time);
@@ -276,8 +281,10 @@ __global__ void __launch_bounds__(kSBlock, MB) render_sorted(const __grid_consta
         }
         accum[idx] = out;
     }
-    for (int o = 16; o > 0; o >>= 1) rays += __shfl_down_sync(0xffffffffu, rays, o);
-    if (lane == 0 && rays) atomicAdd(ray_counter, rays);
+    unsigned long long warp_rays = 0;
+    for (int p = tid; p < kSPix; p += kSBlock) warp_rays += prays[p];
+    for (int o = 16; o > 0; o >>= 1) warp_rays += __shfl_down_sync(0xffffffffu, warp_rays, o);
+    if (lane == 0 && warp_rays) atomicAdd(ray_counter, warp_rays);
 }
 
 namespace {
@@ -299,7 +306,10 @@ cudaError_t launch_sorted_t(const DevScene& sc, const DevRenderParams& rp, float
 }
 }  // namespace
 
-bool sorted_supports(const DevRenderParams& rp) { return rp.spp_count <= (1 << 23) && rp.max_depth < (1 << 24); }
+// spp * max_depth < 2^32: the per-pixel count of color() invocations is 32 bits
+bool sorted_supports(const DevRenderParams& rp) {
+    return rp.spp_count <= (1 << 23) && rp.max_depth < (1 << 16) && (unsigned long long)rp.spp_count * (unsigned long long)rp.max_depth < (1ull << 32);
+}
 
 cudaError_t launch_render_sorted(const DevScene& sc, const DevRenderParams& rp, float4* accum, unsigned long long* counter,
                                  cudaStream_t st) {
