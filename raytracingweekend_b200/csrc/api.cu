@@ -650,9 +650,34 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
                 stack4_need = std::max(stack4_need, need);
             }
     }
+    // Exact traversal-stack needs of the binary trees: a node pushes one reference when both of its children are hit, so a
+    // tree needs as many entries as the most two-child nodes on any root-to-leaf path.  The render kernels of the binary
+    // variants walk all tree items in one loop (bvh_hit_items): the k-th tree item of the world is walked with k-1 ENTER
+    // markers still below it.  Shared memory per block decides whether three blocks fit the 196 KB carve-out (60 KB of L1)
+    // or need the 228 KB one (28 KB): on the Book-2 final scene that is 0.473 vs 0.434 Gpaths/s, so no slack entries.
+    std::function<int(int)> push_need = [&](int ref) -> int {
+        if (ref < 0) return 0;
+        const DevNode& n = nodes[ref];
+        int l, r;
+        memcpy(&l, &n.llo.w, 4), memcpy(&r, &n.lhi.w, 4);
+        const bool two = n.rlo.x <= n.rhi.x;
+        const int nl = push_need(l);
+        return two ? 1 + std::max(nl, push_need(r)) : nl;
+    };
+    int stack_exact = 0, stack_render = 0;
+    {
+        int k = 0;
+        for (int i = 0; i < fs->n_world_items; i++)
+            if (items[i].type == RTW_ITEM_BVH) {
+                stack_exact = std::max(stack_exact, push_need(items[i].first));
+                stack_render = std::max(stack_render, push_need(items[i].end) + k);
+                k++;
+            }
+        stack_render = std::max(stack_render, k);  // all markers are pushed before the first is popped
+    }
     if (getenv("RTW_DEBUG_TREES"))
-        fprintf(stderr, "rtw trees: %zu binary nodes (depth %d), %zu 4-wide nodes (stack need %d), %zu leaves\n", nodes.size(), max_depth,
-                nodes4.size(), stack4_need, leaves.size());
+        fprintf(stderr, "rtw trees: %zu binary nodes (depth %d; stack need: exact %d, render %d), %zu 4-wide nodes (stack need %d), %zu leaves\n",
+                nodes.size(), max_depth, stack_exact, stack_render, nodes4.size(), stack4_need, leaves.size());
     if (dry_run) {
         set_error("scene_create: RTW_DRY_RUN is set (diagnostics only, nothing was uploaded)");
         return nullptr;
@@ -729,8 +754,8 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
         if (k == SEC_NODES4) hot_bytes = (uint32_t)total;
     }
     if (total == 0) total = 16;
-    if (total > 0x7fffffffu) {
-        set_error("scene_create: scene too large for 31-bit blob offsets");
+    if (total > 0x3fffffffu) {  // leaf references ~offset stay above -2^30; below that are the traversal's markers
+        set_error("scene_create: scene too large for 30-bit blob offsets");
         return nullptr;
     }
     // indices -> byte offsets
@@ -797,7 +822,9 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
     d.hot_bytes = hot_bytes, d.all_bytes = (uint32_t)blob.size();
     d.n_world_items = fs->n_world_items, d.n_items = fs->n_items, d.n_prims = fs->n_prims, d.n_lights = fs->n_lights;
     d.render_type = fs->render_type, d.background_type = fs->background_type;
-    d.features = feat, d.max_bvh_depth = max_depth, d.bvh4_stack = stack4_need;
+    d.features = feat, d.stack_exact = stack_exact, d.stack_render = stack_render, d.bvh4_stack = stack4_need;
+    d.n_bvh_items = 0;
+    for (int i = 0; i < fs->n_world_items; i++) d.n_bvh_items += items[i].type == RTW_ITEM_BVH;
     // RTW_FLAG_AUTO: the multi-kernel wavefront pipeline beat the lane-owns-a-path megakernel on noise-textured and on
     // media + BVH scenes; the material-sorted megakernel is faster than both on every measured class, so
     // AUTO only falls back to the wavefront rule when the sorted kernel is switched off.

@@ -145,8 +145,10 @@ struct DevScene {
     int32_t n_world_items, n_items, n_prims, n_lights;
     int32_t render_type, background_type;
     uint32_t features;
-    int32_t max_bvh_depth;  // binary trees (reference topology and SAH): traversal stack entries = depth + 2
+    int32_t stack_exact;    // binary trees, reference topology (intersect_batch): most references ever pushed at once
+    int32_t stack_render;   // binary render trees walked in one loop, ENTER markers included (bvh_hit_items)
     int32_t bvh4_stack;     // 4-wide render trees: most references ever pushed at once
+    int32_t n_bvh_items;    // tree items among the world items
     DevCamera cam;
 };
 

@@ -1,6 +1,7 @@
 // rt_stage.cuh — shared-memory staging of the scene blob and the kernel-variant dispatch shared by kernels.cu and
 // wavefront.cu.
 #pragma once
+#include <cstdlib>
 #include "rt_path.cuh"
 
 namespace rtw {
@@ -69,7 +70,9 @@ inline Launch plan(const DevScene& sc, int block, bool exact = false) {
     // instantiated combinations: every variant at stage 2; {moving, all} at stages 1 and 0
     if (l.stage < 2 && l.variant != kVariants[1]) l.variant = F_ALL;
     size_t staged = l.stage == 2 ? sc.all_bytes : (l.stage == 1 ? sc.hot_bytes : 0);
-    const int entries = (exact || !bvh4_variant(l.variant)) ? sc.max_bvh_depth + 2 : sc.bvh4_stack + 1;
+    // exact needs computed at upload (api.cu push_need), + 1 entry of slack
+    int entries = 1 + (exact ? sc.stack_exact : (bvh4_variant(l.variant) ? sc.bvh4_stack : sc.stack_render));
+    if (const char* extra = getenv("RTW_STACK_EXTRA")) entries += atoi(extra);  // diagnostics: cost of a deeper stack
     size_t stack = (l.variant & F_BVH) ? (size_t)entries * block * sizeof(int) : 0;
     l.smem = staged + stack;
     return l;

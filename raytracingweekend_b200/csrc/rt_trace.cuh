@@ -7,6 +7,9 @@ namespace rtw {
 #ifndef RTW_BVH4
 #define RTW_BVH4 1  // render kernels walk the 4-wide tree where it was measured faster (A/B switch: 0 = never, 2 = always)
 #endif
+#ifndef RTW_UNIFIED_BVH
+#define RTW_UNIFIED_BVH 1  // binary-tree render variants walk all bvh_node items of the world in one loop (A/B switch)
+#endif
 #ifndef RTW_BVH4_OCTANT
 #define RTW_BVH4_OCTANT 1
 #endif
@@ -207,6 +210,95 @@ RTW_DEV void bvh4_hit(const SceneView& sv, int root, const RayK& rk, float time,
     }
 }
 
+// All bvh_node items of the world in ONE traversal loop (render kernels of the binary-tree variants).  closest_hit defers
+// the tree items: it pushes an ENTER marker per item and this loop pops them like any other reference — a lane that
+// finishes one tree enters the next (ray into that item's frame) while its neighbours are still inside the previous
+// one.  A warp then waits for its longest lane ONCE, max_i(steps_A(i) + steps_B(i)), instead of once per tree,
+// max_i steps_A(i) + max_i steps_B(i): on the Book-2 final scene four warps out of five hold a lane or two that enter the
+// small sphere-cluster tree, and walked it at 1-2 active lanes after everyone had waited for the ground tree.
+// Same boxes, same leaves, same tie rule as bvh_hit; the items see the closest hit of the lists and of each other as
+// their cull distance, which can only shorten the walk.  `h` carries the closest hit so far in and the result out.
+constexpr int kBvhEnter = (int)0x80000001;  // ENTER marker of item i = kBvhEnter + i; markers and kBvhDone are < -2^30
+#ifndef RTW_UNIFIED_INLINE
+#define RTW_UNIFIED_INLINE 1  // A/B switch (0 = one out-of-line copy)
+#endif
+#if RTW_UNIFIED_INLINE
+#define RTW_UNIFIED_FN RTW_DEV
+#else
+#define RTW_UNIFIED_FN __device__ __noinline__
+#endif
+template <uint32_t F, int SM>
+RTW_UNIFIED_FN HitId bvh_hit_items(uint32_t items0, SceneView sv, RayK rk, float time, float tmin, HitId h, int* stack, int stride, int sp) {
+    const float tmax = h.t;
+    float best = tmax;
+    int best_prim = -1, best_leaf = 0, best_item = -1;
+    RayK lk = rk;
+    int cur_item = -1;
+    sp--;
+    int ref = stack[sp * stride];
+    for (;;) {
+        while (ref >= 0) {  // inner node: test both child boxes (as in bvh_hit)
+            const float4 llo = hot4<SM>(sv, (uint32_t)ref), lhi = hot4<SM>(sv, (uint32_t)ref + 16);
+            const float4 rlo = hot4<SM>(sv, (uint32_t)ref + 32), rhi = hot4<SM>(sv, (uint32_t)ref + 48);
+            const float cull = best_prim >= 0 ? fmaf(best, 4e-6f, best) : tmax;
+            float tl, tr;
+            const bool hl = aabb_hit(llo, lhi, lk.o, lk.inv, tmin, cull, tl);
+            const bool hr = aabb_hit(rlo, rhi, lk.o, lk.inv, tmin, cull, tr);
+            const int l = fi(llo.w), r = fi(lhi.w);
+            if (hl && hr) {
+                const bool left_first = !(tr < tl);
+                stack[sp * stride] = left_first ? r : l;
+                sp++;
+                ref = left_first ? l : r;
+            } else if (hl || hr) {
+                ref = hl ? l : r;
+            } else if (sp > 0) {
+                sp--;
+                ref = stack[sp * stride];
+            } else {
+                ref = kBvhDone;
+            }
+        }
+        if (ref < -0x40000000) {
+            if (ref == kBvhDone) break;
+            // ENTER: the next tree item
+            cur_item = ref - kBvhEnter;
+            const float4 i0 = hot4<SM>(sv, items0 + (uint32_t)cur_item * 32u);
+            const int ixf = fi(i0.y);
+            lk = rk;
+            if (ixf >= 0) lk = xf_rayk(ld_xf<SM>(sv, (uint32_t)ixf), rk);
+            ref = fi(i0.w);  // DevItem.end: the render tree
+            continue;
+        }
+        {  // leaf: list semantics against the closest hit of the non-tree items
+            const uint2 lf = hot2<SM>(sv, (uint32_t)~ref);
+            float t_leaf = tmax;
+            int p_leaf = -1;
+            test_groups<F, SM, true>(sv, lf.x, lf.y, lk, time, tmin, t_leaf, p_leaf);
+            const int leaf = ~ref;
+            if (p_leaf >= 0 && (best_prim < 0 || t_leaf < best || (t_leaf == best && leaf >= best_leaf))) {
+                best = t_leaf;
+                best_prim = p_leaf;
+                best_leaf = leaf;
+                best_item = cur_item;
+            }
+            if (sp > 0) {
+                sp--;
+                ref = stack[sp * stride];
+            } else {
+                ref = kBvhDone;
+            }
+        }
+        if (ref == kBvhDone) break;
+    }
+    if (best_prim >= 0) {
+        h.t = best;
+        h.prim = best_prim;
+        h.item = best_item;
+    }
+    return h;
+}
+
 // world.hit(r, tmin, tmax) (RayTracingWeekend.cpp:52 -> hittable_list.h:11-37) over the flattened items.
 // `rng` == nullptr skips constant_medium items (intersect_batch: media are stochastic).
 // EXACT_TIES replays the second pass of hittable_list::hit (hittable_list.h:26-34) for scenes with bvh_node items:
@@ -224,6 +316,11 @@ RTW_DEV HitId closest_hit(const DevScene& sc, const SceneView& sv, V3 o, V3 d, f
     const RayK rk = make_rayk(o, d);
     const uint32_t items0 = sc.off[SEC_ITEMS];
     constexpr bool kOnlyLists = (F & (F_BVH | F_MEDIA)) == 0;
+    // big (unstaged) scenes only: a small staged scene compiled from the same variant (Cornell smoke: no trees at all) loses
+    // 4 % to the longer hot path, and calling the loop out of line gives the gain back on the Book-2 final scene
+    // (0.484 inline / 0.463 out of line / 0.471 one tree after the other, Gpaths/s)
+    constexpr bool kUnified = RTW_UNIFIED_BVH && !EXACT_TIES && (F & F_BVH) != 0 && !bvh4_variant(F) && SM < 2;
+    int deferred = 0;  // kUnified: tree items wait on the traversal stack (bvh_hit_items)
 #pragma unroll 1
     for (int it = 0; it < sc.n_world_items; it++) {
         const uint32_t ia = items0 + (uint32_t)it * 32u;
@@ -233,7 +330,10 @@ RTW_DEV HitId closest_hit(const DevScene& sc, const SceneView& sv, V3 o, V3 d, f
             int before = h.prim;
             test_groups<F, SM, !EXACT_TIES>(sv, (uint32_t)first, (uint32_t)end, rk, time, tmin, h.t, h.prim);
             if (h.prim != before) h.item = it;
-        } else if ((F & F_BVH) && type == RTW_ITEM_BVH) {
+        } else if (kUnified && type == RTW_ITEM_BVH) {
+            stack[deferred * stride] = kBvhEnter + it;
+            deferred++;
+        } else if (!kUnified && (F & F_BVH) && type == RTW_ITEM_BVH) {
             RayK lk = rk;
             if (ixf >= 0) lk = xf_rayk(ld_xf<SM>(sv, (uint32_t)ixf), rk);
             int p = -1;
@@ -286,6 +386,9 @@ RTW_DEV HitId closest_hit(const DevScene& sc, const SceneView& sv, V3 o, V3 d, f
                 h.item = it;
             }
         }
+    }
+    if constexpr (kUnified) {
+        if (deferred > 0) h = bvh_hit_items<F, SM>(items0, sv, rk, time, tmin, h, stack, stride, deferred);
     }
     if (EXACT_TIES && (F & F_BVH) && h.prim >= 0) {
 #pragma unroll 1

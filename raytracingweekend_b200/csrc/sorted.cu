@@ -26,6 +26,7 @@
 // float side accumulator (NaN / Inf propagate like in the reference).  HBM traffic is unchanged: one 16-byte
 // store per pixel per launch.
 #include <cstdio>
+#include <cstdlib>
 
 #include "kernels.hpp"
 #include "rt_path.cuh"
@@ -301,6 +302,12 @@ cudaError_t launch_sorted_t(const DevScene& sc, const DevRenderParams& rp, float
     const size_t bytes = pool_off + sorted_pool_bytes(PT);
     cudaError_t e = cudaFuncSetAttribute(render_sorted<F, SM, PT, MB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
     if (e != cudaSuccess) return e;
+    if (getenv("RTW_DEBUG_TREES")) {
+        int nb = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, render_sorted<F, SM, PT, MB>, kSBlock, bytes);
+        fprintf(stderr, "rtw render_sorted<%u,%d,%d,%d>: %zu bytes of shared memory per block (stack %zu), %d blocks/SM\n", F, SM, PT, MB, bytes,
+                smem, nb);
+    }
     render_sorted<F, SM, PT, MB><<<tiles_x * tiles_y, kSBlock, bytes, st>>>(sc, rp, accum, counter, pool_off);
     return cudaGetLastError();
 }
