@@ -296,12 +296,21 @@ cudaError_t launch_sorted_t(const DevScene& sc, const DevRenderParams& rp, float
 #define RTW_SORTED_BVH_PT 2
 #endif
     constexpr int PT = (F == kVariants[0]) ? 2 : ((F & F_BVH) ? RTW_SORTED_BVH_PT : 3);
-    constexpr int MB = (F == kVariants[0]) ? 4 : ((F & F_BVH) && PT == 4 ? 2 : 3);
+#ifndef RTW_SORTED_ALL_MB
+#define RTW_SORTED_ALL_MB 2
+#endif
+#ifndef RTW_SORTED_MB2_COND
+#define RTW_SORTED_MB2_COND ((F & F_BVH) && SM < 2)
+#endif
+    constexpr int MB = (F == kVariants[0]) ? 4 : ((F & F_BVH) && PT == 4 ? 2 : (RTW_SORTED_MB2_COND ? RTW_SORTED_ALL_MB : 3));
     const int tiles_x = (rp.nx + kSTile - 1) / kSTile, tiles_y = (rp.ny + kSTile - 1) / kSTile;
     const uint32_t pool_off = (uint32_t)((smem + 15) & ~(size_t)15);
     const size_t bytes = pool_off + sorted_pool_bytes(PT);
     cudaError_t e = cudaFuncSetAttribute(render_sorted<F, SM, PT, MB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
     if (e != cudaSuccess) return e;
+#ifdef RTW_SORTED_CARVEOUT
+    if (RTW_SORTED_MB2_COND) cudaFuncSetAttribute(render_sorted<F, SM, PT, MB>, cudaFuncAttributePreferredSharedMemoryCarveout, RTW_SORTED_CARVEOUT);
+#endif
     if (getenv("RTW_DEBUG_TREES")) {
         int nb = 0;
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, render_sorted<F, SM, PT, MB>, kSBlock, bytes);
