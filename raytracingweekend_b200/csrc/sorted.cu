@@ -37,11 +37,14 @@ namespace rtw {
 constexpr int kSBlock = 256;
 constexpr int kSTile = 16;  // 16 x 16 pixels per block
 constexpr int kSPix = kSTile * kSTile;
-// PT = path slots per thread.  The pool size trades queue fill (whole 32-path units per class) against resident blocks:
-// PT = 2 -> 512 slots, 49 KB: 4 blocks/SM at <= 64 registers for the Cornell-class variant (+7 % there); 3 blocks/SM at
-//           80 registers for the BVH variants, whose traversal stacks take another 10-20 KB per block and which are
-//           latency-bound (Book-2 final +19 %, random balls +11 % over PT = 3 at 2 blocks/SM);
-// PT = 3 -> 768 slots, 71 KB, 3 blocks/SM at <= 80 registers (texture variant: it spills at 64 registers).
+// PT = path slots per thread, MB = resident blocks per SM (launch bounds -> registers).  Measured choices
+// (profiles/r1_ab_blocks_per_sm_bvh.txt, r1_ab_pool_tex.txt), set in launch_sorted_t:
+//   Cornell-class variant (F_XF only):       PT 2 (512 slots, 49 KB), MB 4: 64 registers, issue-bound, wants warps;
+//   texture variant (Perlin, image, checker): PT 3 (768 slots, 71 KB), MB 2: 128 registers — the 80-register build of
+//                                            MB 3 spilled; Perlin 7.10 -> 7.40, checker spheres 5.18 -> 5.42 Gpaths/s;
+//   BVH variants on unstaged scenes:         PT 2, MB 2: 128 registers, no spills, and two 64 KB blocks leave ~100 KB
+//                                            of L1 for the nodes and records (Book-2 final 0.485 -> 0.59);
+//   all-features variant on staged scenes:   PT 2, MB 3 (Cornell smoke: 4.12 vs 3.32 at MB 2).
 __host__ __device__ constexpr int pool_slots(int pt) { return kSBlock * pt; }
 __host__ __device__ constexpr int queue_cap(int pt) { return pool_slots(pt) <= 512 ? 512 : 1024; }  // ring capacity per class (power of two >= slots)
 __host__ __device__ constexpr int min_blocks(int pt) { return pt <= 2 ? 4 : (pt == 3 ? 3 : 2); }
@@ -295,14 +298,20 @@ cudaError_t launch_sorted_t(const DevScene& sc, const DevRenderParams& rp, float
 #ifndef RTW_SORTED_BVH_PT
 #define RTW_SORTED_BVH_PT 2
 #endif
-    constexpr int PT = (F == kVariants[0]) ? 2 : ((F & F_BVH) ? RTW_SORTED_BVH_PT : 3);
+#ifndef RTW_SORTED_TEX_PT
+#define RTW_SORTED_TEX_PT 3
+#endif
+#ifndef RTW_SORTED_TEX_MB
+#define RTW_SORTED_TEX_MB 2
+#endif
+    constexpr int PT = (F == kVariants[0]) ? 2 : ((F & F_BVH) ? RTW_SORTED_BVH_PT : RTW_SORTED_TEX_PT);
 #ifndef RTW_SORTED_ALL_MB
 #define RTW_SORTED_ALL_MB 2
 #endif
 #ifndef RTW_SORTED_MB2_COND
 #define RTW_SORTED_MB2_COND ((F & F_BVH) && SM < 2)
 #endif
-    constexpr int MB = (F == kVariants[0]) ? 4 : ((F & F_BVH) && PT == 4 ? 2 : (RTW_SORTED_MB2_COND ? RTW_SORTED_ALL_MB : 3));
+    constexpr int MB = (F == kVariants[0]) ? 4 : ((F & F_BVH) && PT == 4 ? 2 : (RTW_SORTED_MB2_COND ? RTW_SORTED_ALL_MB : ((F & F_BVH) ? 3 : RTW_SORTED_TEX_MB)));
     const int tiles_x = (rp.nx + kSTile - 1) / kSTile, tiles_y = (rp.ny + kSTile - 1) / kSTile;
     const uint32_t pool_off = (uint32_t)((smem + 15) & ~(size_t)15);
     const size_t bytes = pool_off + sorted_pool_bytes(PT);
