@@ -260,6 +260,8 @@ def run_ours(args) -> None:
         dt = time.perf_counter() - t0
         s2.close()
         b2.close()
+        if os.environ.get("RTW_BENCH_DEBUG"):
+            sys.stderr.write(f"e2e pass {it}: {dt * 1e3:.2f} ms\n")
         if it > 0:
             e2e_times.append(dt)
     te = torch.tensor([sum(e2e_times)], dtype=torch.float64, device=dev)

@@ -45,7 +45,7 @@ constexpr int kSPix = kSTile * kSTile;
 //   BVH variants on unstaged scenes:         PT 2, MB 2: 128 registers, no spills, and two 64 KB blocks leave ~100 KB
 //                                            of L1 for the nodes and records (Book-2 final 0.485 -> 0.59);
 //   all-features variant on staged scenes:   PT 2, MB 3 (Cornell smoke: 4.12 vs 3.32 at MB 2).
-__host__ __device__ constexpr int pool_slots(int pt) { return kSBlock * pt; }
+__host__ __device__ constexpr int pool_slots(int pt) { return 256 * pt; }
 __host__ __device__ constexpr int queue_cap(int pt) { return pool_slots(pt) <= 512 ? 512 : 1024; }  // ring capacity per class (power of two >= slots)
 __host__ __device__ constexpr int min_blocks(int pt) { return pt <= 2 ? 4 : (pt == 3 ? 3 : 2); }
 
@@ -65,8 +65,9 @@ constexpr size_t sorted_pool_bytes(int pt) {
     return (size_t)pool_slots(pt) * 64 + (size_t)C_QUEUES * queue_cap(pt) * 2 + (size_t)kSPix * (3 * (8 + 4) + 4) + sizeof(SortedCtl) + 64;
 }
 
-template <uint32_t F, int SM, int PT, int MB>
-__global__ void __launch_bounds__(kSBlock, MB) render_sorted(const __grid_constant__ DevScene sc,
+// BS = threads per block (a multiple of 32; the pixel tile and the pool do not depend on it)
+template <uint32_t F, int SM, int PT, int MB, int BS>
+__global__ void __launch_bounds__(BS, MB) render_sorted(const __grid_constant__ DevScene sc,
                                                                               const __grid_constant__ DevRenderParams rp,
                                                                               float4* __restrict__ accum,
                                                                               unsigned long long* __restrict__ ray_counter,
@@ -108,11 +109,11 @@ __global__ void __launch_bounds__(kSBlock, MB) render_sorted(const __grid_consta
         }
     };
 
-    for (int k = tid; k < 3 * kSPix; k += kSBlock) fx[k] = 0ull, fl[k] = 0.0f;
-    for (int k = tid; k < kSPix; k += kSBlock) prays[k] = 0u;
-    for (int k = tid; k < C_QUEUES * kQCap; k += kSBlock) queue[k] = kQEmpty;
+    for (int k = tid; k < 3 * kSPix; k += BS) fx[k] = 0ull, fl[k] = 0.0f;
+    for (int k = tid; k < kSPix; k += BS) prays[k] = 0u;
+    for (int k = tid; k < C_QUEUES * kQCap; k += BS) queue[k] = kQEmpty;
     __syncthreads();
-    for (int s = tid; s < kSPool; s += kSBlock) queue[C_REGEN * kQCap + s] = (uint16_t)s;  // every slot needs a camera ray
+    for (int s = tid; s < kSPool; s += BS) queue[C_REGEN * kQCap + s] = (uint16_t)s;  // every slot needs a camera ray
     if (tid < 8) ctl->head[tid] = 0, ctl->tail[tid] = (tid == C_REGEN) ? kSPool : 0;
     if (tid == 8) ctl->item_next = 0, ctl->live = kSPool;
     __syncthreads();
@@ -231,7 +232,7 @@ __global__ void __launch_bounds__(kSBlock, MB) render_sorted(const __grid_consta
         int ncls = (c >= C_TERM) ? C_DEAD : C_REGEN;  // a terminal/regen lane only stays dead when the pool is empty
         if (alive) {
             bounce++;
-            const HitId hit = closest_hit<F, SM, false>(sc, sv, ray.o, ray.d, ray.time, 0.001f, FLT_MAX, &rng, bounce, stack, kSBlock);
+            const HitId hit = closest_hit<F, SM, false>(sc, sv, ray.o, ray.d, ray.time, 0.001f, FLT_MAX, &rng, bounce, stack, BS);
             ncls = C_TERM;
             if (hit.prim != -1 && sc.render_type != RTW_RENDER_NORMAL) {
                 uint32_t pm;
@@ -270,7 +271,7 @@ __global__ void __launch_bounds__(kSBlock, MB) render_sorted(const __grid_consta
 #endif
 
     // one 16-byte store per pixel (canvas[j*nx+i], RayTracingWeekend.cpp:247)
-    for (int p = tid; p < n_pix; p += kSBlock) {
+    for (int p = tid; p < n_pix; p += BS) {
         int pi, pj;
         slot_pixel((uint32_t)p, pi, pj);
         const size_t idx = (size_t)pj * rp.nx + pi;
@@ -286,7 +287,7 @@ __global__ void __launch_bounds__(kSBlock, MB) render_sorted(const __grid_consta
         accum[idx] = out;
     }
     unsigned long long warp_rays = 0;
-    for (int p = tid; p < kSPix; p += kSBlock) warp_rays += prays[p];
+    for (int p = tid; p < kSPix; p += BS) warp_rays += prays[p];
     for (int o = 16; o > 0; o >>= 1) warp_rays += __shfl_down_sync(0xffffffffu, warp_rays, o);
     if (lane == 0 && warp_rays) atomicAdd(ray_counter, warp_rays);
 }
@@ -312,21 +313,28 @@ cudaError_t launch_sorted_t(const DevScene& sc, const DevRenderParams& rp, float
 #define RTW_SORTED_MB2_COND ((F & F_BVH) && SM < 2)
 #endif
     constexpr int MB = (F == kVariants[0]) ? 4 : ((F & F_BVH) && PT == 4 ? 2 : (RTW_SORTED_MB2_COND ? RTW_SORTED_ALL_MB : ((F & F_BVH) ? 3 : RTW_SORTED_TEX_MB)));
+#ifndef RTW_SORTED_BVH_BS
+#define RTW_SORTED_BVH_BS 256
+#endif
+    constexpr int BS = RTW_SORTED_MB2_COND ? RTW_SORTED_BVH_BS : kSBlock;
+    // `smem` (staged bytes + traversal stacks) was planned for kSBlock threads: the stacks scale with the block size
+    const size_t staged = SM == 2 ? sc.all_bytes : (SM == 1 ? sc.hot_bytes : 0);
+    smem = staged + (smem - staged) / kSBlock * BS;
     const int tiles_x = (rp.nx + kSTile - 1) / kSTile, tiles_y = (rp.ny + kSTile - 1) / kSTile;
     const uint32_t pool_off = (uint32_t)((smem + 15) & ~(size_t)15);
     const size_t bytes = pool_off + sorted_pool_bytes(PT);
-    cudaError_t e = cudaFuncSetAttribute(render_sorted<F, SM, PT, MB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    cudaError_t e = cudaFuncSetAttribute(render_sorted<F, SM, PT, MB, BS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
     if (e != cudaSuccess) return e;
 #ifdef RTW_SORTED_CARVEOUT
-    if (RTW_SORTED_MB2_COND) cudaFuncSetAttribute(render_sorted<F, SM, PT, MB>, cudaFuncAttributePreferredSharedMemoryCarveout, RTW_SORTED_CARVEOUT);
+    if (RTW_SORTED_MB2_COND) cudaFuncSetAttribute(render_sorted<F, SM, PT, MB, BS>, cudaFuncAttributePreferredSharedMemoryCarveout, RTW_SORTED_CARVEOUT);
 #endif
     if (getenv("RTW_DEBUG_TREES")) {
         int nb = 0;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, render_sorted<F, SM, PT, MB>, kSBlock, bytes);
-        fprintf(stderr, "rtw render_sorted<%u,%d,%d,%d>: %zu bytes of shared memory per block (stack %zu), %d blocks/SM\n", F, SM, PT, MB, bytes,
-                smem, nb);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, render_sorted<F, SM, PT, MB, BS>, BS, bytes);
+        fprintf(stderr, "rtw render_sorted<%u,%d,%d,%d,%d>: %zu bytes of shared memory per block (stack %zu), %d blocks/SM\n", F, SM, PT, MB, BS,
+                bytes, smem - staged, nb);
     }
-    render_sorted<F, SM, PT, MB><<<tiles_x * tiles_y, kSBlock, bytes, st>>>(sc, rp, accum, counter, pool_off);
+    render_sorted<F, SM, PT, MB, BS><<<tiles_x * tiles_y, BS, bytes, st>>>(sc, rp, accum, counter, pool_off);
     return cudaGetLastError();
 }
 }  // namespace
