@@ -34,7 +34,7 @@ SPP = 1024
 MAX_DEPTH = 100
 # SURVEY §8d / DESIGN.md §5: algorithmic FP32 flops per path of the reference's math on this scene, counted by the
 # instrumented oracle (tools/count_flops.py: oracle_events_*, 64x64x64 spp sample, Appendix D cost table).
-NCU_DRAM_BYTES_PER_LAUNCH = 360704 + 0  # read + write (the image is still in L2 when the kernel ends), see roofline.traffic below
+NCU_DRAM_BYTES_PER_LAUNCH = 49664 + 1280  # read + write (the image is still in L2 when the kernel ends), see roofline.traffic below
 FLOP_PER_PATH = 1344.5
 FP32_PEAK_SPEC_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12  # 74.4
 
@@ -296,18 +296,18 @@ def run_ours(args) -> None:
                 "frac": achieved / peak.value if peak.value else None,
                 # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch over the whole 1024x1024 image (256 spp; the traffic
                 # is the scene read and the image store and does not grow with spp), from the ncu
-                # --set full capture summarised in profiles/r1_sorted_v8_cornell_ncu_details.txt; the 16 MB image was still
+                # --set full capture summarised in profiles/r1_sorted_v11_cornell_ncu_details.txt; the 16 MB image was still
                 # in L2 when the kernel ended.  Only valid for the single-GPU shape of that capture.
                 "traffic": NCU_DRAM_BYTES_PER_LAUNCH if world == 1 and sorted_kernel and (NX, NY) == (1024, 1024) else None,
-                "traffic_unit": "bytes per launch (ncu, profiles/r1_sorted_v8_cornell_ncu_details.txt)",
+                "traffic_unit": "bytes per launch (ncu, profiles/r1_sorted_v11_cornell_ncu_details.txt)",
                 "peak_source": "FFMA micro-benchmark run in this process (rtw_measure_fp32_peak); spec-derived "
                                f"{FP32_PEAK_SPEC_TFLOPS:.1f} TFLOP/s at 1965 MHz",
                 "frac_of_spec": achieved / FP32_PEAK_SPEC_TFLOPS,
                 "algorithmic_flop_per_path": fpp,
                 # the roofline this kernel actually sits under is warp-instruction ISSUE (one per scheduler per cycle, every
-                # opcode): ncu sm__inst_issued / issue slots of the cfg4 capture (profiles/r1_sorted_v8_cornell_ncu_details.txt);
+                # opcode): ncu sm__inst_issued / issue slots of the cfg4 capture (profiles/r1_sorted_v11_cornell_ncu_details.txt);
                 # the algorithmic count above excludes compares, selects, address/loop arithmetic and the Philox integer rounds
-                "issue_slots_busy_ncu": 0.788 if sorted_kernel and (NX, NY) == (1024, 1024) else None,
+                "issue_slots_busy_ncu": 0.801 if sorted_kernel and (NX, NY) == (1024, 1024) else None,
                 "kernel": "render_sorted (material-sorted megakernel, csrc/sorted.cu)" if sorted_kernel else "render_megakernel",
                 "kernel_ms_per_launch": kern_ms / args.steps,
                 "hbm": {"algorithmic_bytes_per_launch": NX * NY * 16, "achieved_gbs": NX * NY * 16 / (kern_ms / args.steps * 1e-3) / 1e9,

@@ -5,7 +5,8 @@
 // shared memory instead of registers, and the warps of a block exchange paths through per-class queues so that a
 // warp always shades 32 paths of ONE material class and then traces their 32 new rays:
 //
-//   block  = 256 threads, one 16x16 pixel tile, one pool of (pixel, sample) items like the warp pool of kernels.cu
+//   block  = 256 or 512 threads (per variant, launch_sorted_t), one 16x16 pixel tile, one pool of (pixel, sample) items like the
+//            warp pool of kernels.cu
 //   slots  = kSPool path slots in shared memory, 64 B each: (o, t) (d, time) (beta, prim) (item, pixel, sample, bounce)
 //   queues = one ring of slot ids per class in shared memory {lambertian, dielectric, metal, isotropic, terminal
 //            (miss / emitter), needs-a-camera-ray}; producers reserve with one atomicAdd per (warp, class) found by
@@ -39,7 +40,9 @@ constexpr int kSTile = 16;  // 16 x 16 pixels per block
 constexpr int kSPix = kSTile * kSTile;
 // PT = path slots per thread, MB = resident blocks per SM (launch bounds -> registers).  Measured choices
 // (profiles/r1_ab_blocks_per_sm_bvh.txt, r1_ab_pool_tex.txt), set in launch_sorted_t:
-//   Cornell-class variant (F_XF only):       PT 2 (512 slots, 49 KB), MB 4: 64 registers, issue-bound, wants warps;
+//   Cornell-class variant (F_XF only):       512 threads, PT 4 (1024 slots, 88 KB), MB 2: 64 registers, issue-bound, wants
+//                                            warps (32 per SM) and a big pool (whole units per class): 6.40 -> 6.53 Gpaths/s
+//                                            over 256 threads / 512 slots / MB 4; fewer blocks at more registers all lose;
 //   texture variant (Perlin, image, checker): PT 3 (768 slots, 71 KB), MB 2: 128 registers — the 80-register build of
 //                                            MB 3 spilled; Perlin 7.10 -> 7.40, checker spheres 5.18 -> 5.42 Gpaths/s;
 //   BVH variants on unstaged scenes:         PT 2, MB 2: 128 registers, no spills, and two 64 KB blocks leave ~100 KB
@@ -305,18 +308,27 @@ cudaError_t launch_sorted_t(const DevScene& sc, const DevRenderParams& rp, float
 #ifndef RTW_SORTED_TEX_MB
 #define RTW_SORTED_TEX_MB 2
 #endif
-    constexpr int PT = (F == kVariants[0]) ? 2 : ((F & F_BVH) ? RTW_SORTED_BVH_PT : RTW_SORTED_TEX_PT);
+#ifndef RTW_SORTED_CORNELL_PT
+#define RTW_SORTED_CORNELL_PT 4
+#endif
+#ifndef RTW_SORTED_CORNELL_MB
+#define RTW_SORTED_CORNELL_MB 2
+#endif
+    constexpr int PT = (F == kVariants[0]) ? RTW_SORTED_CORNELL_PT : ((F & F_BVH) ? RTW_SORTED_BVH_PT : RTW_SORTED_TEX_PT);
 #ifndef RTW_SORTED_ALL_MB
 #define RTW_SORTED_ALL_MB 2
 #endif
 #ifndef RTW_SORTED_MB2_COND
 #define RTW_SORTED_MB2_COND ((F & F_BVH) && SM < 2)
 #endif
-    constexpr int MB = (F == kVariants[0]) ? 4 : ((F & F_BVH) && PT == 4 ? 2 : (RTW_SORTED_MB2_COND ? RTW_SORTED_ALL_MB : ((F & F_BVH) ? 3 : RTW_SORTED_TEX_MB)));
+    constexpr int MB = (F == kVariants[0]) ? RTW_SORTED_CORNELL_MB : ((F & F_BVH) && PT == 4 ? 2 : (RTW_SORTED_MB2_COND ? RTW_SORTED_ALL_MB : ((F & F_BVH) ? 3 : RTW_SORTED_TEX_MB)));
 #ifndef RTW_SORTED_BVH_BS
 #define RTW_SORTED_BVH_BS 256
 #endif
-    constexpr int BS = RTW_SORTED_MB2_COND ? RTW_SORTED_BVH_BS : kSBlock;
+#ifndef RTW_SORTED_CORNELL_BS
+#define RTW_SORTED_CORNELL_BS 512
+#endif
+    constexpr int BS = RTW_SORTED_MB2_COND ? RTW_SORTED_BVH_BS : (F == kVariants[0] ? RTW_SORTED_CORNELL_BS : kSBlock);
     // `smem` (staged bytes + traversal stacks) was planned for kSBlock threads: the stacks scale with the block size
     const size_t staged = SM == 2 ? sc.all_bytes : (SM == 1 ? sc.hot_bytes : 0);
     smem = staged + (smem - staged) / kSBlock * BS;
