@@ -38,18 +38,24 @@ namespace rtw {
 constexpr int kSBlock = 256;
 constexpr int kSTile = 16;  // 16 x 16 pixels per block
 constexpr int kSPix = kSTile * kSTile;
-// PT = path slots per thread, MB = resident blocks per SM (launch bounds -> registers).  Measured choices
-// (profiles/r1_ab_blocks_per_sm_bvh.txt, r1_ab_pool_tex.txt), set in launch_sorted_t:
-//   Cornell-class variant (F_XF only):       512 threads, PT 4 (1024 slots, 88 KB), MB 2: 64 registers, issue-bound, wants
-//                                            warps (32 per SM) and a big pool (whole units per class): 6.40 -> 6.53 Gpaths/s
-//                                            over 256 threads / 512 slots / MB 4; fewer blocks at more registers all lose;
-//   texture variant (Perlin, image, checker): PT 3 (768 slots, 71 KB), MB 2: 128 registers — the 80-register build of
-//                                            MB 3 spilled; Perlin 7.10 -> 7.40, checker spheres 5.18 -> 5.42 Gpaths/s;
-//   BVH variants on unstaged scenes:         PT 2, MB 2: 128 registers, no spills, and two 64 KB blocks leave ~100 KB
-//                                            of L1 for the nodes and records (Book-2 final 0.485 -> 0.59);
-//   all-features variant on staged scenes:   PT 2, MB 3 (Cornell smoke: 4.12 vs 3.32 at MB 2).
+// BS = threads per block, PT = path slots per 256 threads, MB = resident blocks per SM (launch bounds -> registers).
+// Measured choices (profiles/r1_ab_*.txt), set in launch_sorted_t.  The common thread: ONE big pool per SM shared by many
+// warps keeps the class queues full (whole 32-path units, few waits), as long as the registers suffice:
+//   Cornell-class variant (F_XF only):        512 threads, 1024 slots, 2 blocks/SM: 64 registers, issue-bound, wants 32
+//                                             warps per SM: 6.40 -> 6.53 Gpaths/s over 256 / 512 / 4 blocks; 1024 threads
+//                                             with 2048 slots in one block loses again (6.33);
+//   texture variant (Perlin, image, checker): 768 threads, 1536 slots, 1 block/SM, 85 registers: Perlin 7.41 -> 8.88,
+//                                             checker spheres 5.43 -> 7.53, light_sample 6.78 -> 10.2 over 256 threads /
+//                                             768 slots / 2 blocks (896 threads the same, 512 and 1024 threads less);
+//   BVH variants on unstaged scenes:          256 threads, 512 slots, 2 blocks/SM: 128 registers, no spills, and two 64 KB
+//                                             blocks leave ~100 KB of L1 for nodes and records (Book-2 final 0.485 -> 0.59;
+//                                             bigger pools or blocks lose: they eat the L1);
+//   all-features variant on staged scenes:    256 threads, 512 slots, 3 blocks/SM (Cornell smoke 4.14; 768 threads in one
+//                                             block the same, 512 threads 3.37, 2 blocks of 256 3.32).
 __host__ __device__ constexpr int pool_slots(int pt) { return 256 * pt; }
-__host__ __device__ constexpr int queue_cap(int pt) { return pool_slots(pt) <= 512 ? 512 : 1024; }  // ring capacity per class (power of two >= slots)
+__host__ __device__ constexpr int queue_cap(int pt) {  // ring capacity per class (power of two >= slots)
+    return pool_slots(pt) <= 512 ? 512 : (pool_slots(pt) <= 1024 ? 1024 : 2048);
+}
 __host__ __device__ constexpr int min_blocks(int pt) { return pt <= 2 ? 4 : (pt == 3 ? 3 : 2); }
 
 enum : int { C_LAMB = 0, C_DIEL, C_METAL, C_ISO, C_TERM, C_REGEN, C_QUEUES, C_DEAD = C_QUEUES };
@@ -299,36 +305,24 @@ namespace {
 template <uint32_t F, int SM>
 cudaError_t launch_sorted_t(const DevScene& sc, const DevRenderParams& rp, float4* accum, unsigned long long* counter,
                             size_t smem, cudaStream_t st) {
-#ifndef RTW_SORTED_BVH_PT
-#define RTW_SORTED_BVH_PT 2
+    // threads per block, pool slots per 256 threads, resident blocks per SM — one measured triple per variant class (header
+    // comment), written BS * 1000 + PT * 10 + MB so that -DRTW_CFG_x=... can override a class for A/B builds (tools/ab_libs.sh;
+    // nvcc splits -D values at commas)
+#ifndef RTW_CFG_CORNELL
+#define RTW_CFG_CORNELL 512042
 #endif
-#ifndef RTW_SORTED_TEX_PT
-#define RTW_SORTED_TEX_PT 3
+#ifndef RTW_CFG_TEX
+#define RTW_CFG_TEX 768061
 #endif
-#ifndef RTW_SORTED_TEX_MB
-#define RTW_SORTED_TEX_MB 2
+#ifndef RTW_CFG_BVH_UNSTAGED
+#define RTW_CFG_BVH_UNSTAGED 256022
 #endif
-#ifndef RTW_SORTED_CORNELL_PT
-#define RTW_SORTED_CORNELL_PT 4
+#ifndef RTW_CFG_BVH_STAGED
+#define RTW_CFG_BVH_STAGED 256023
 #endif
-#ifndef RTW_SORTED_CORNELL_MB
-#define RTW_SORTED_CORNELL_MB 2
-#endif
-    constexpr int PT = (F == kVariants[0]) ? RTW_SORTED_CORNELL_PT : ((F & F_BVH) ? RTW_SORTED_BVH_PT : RTW_SORTED_TEX_PT);
-#ifndef RTW_SORTED_ALL_MB
-#define RTW_SORTED_ALL_MB 2
-#endif
-#ifndef RTW_SORTED_MB2_COND
-#define RTW_SORTED_MB2_COND ((F & F_BVH) && SM < 2)
-#endif
-    constexpr int MB = (F == kVariants[0]) ? RTW_SORTED_CORNELL_MB : ((F & F_BVH) && PT == 4 ? 2 : (RTW_SORTED_MB2_COND ? RTW_SORTED_ALL_MB : ((F & F_BVH) ? 3 : RTW_SORTED_TEX_MB)));
-#ifndef RTW_SORTED_BVH_BS
-#define RTW_SORTED_BVH_BS 256
-#endif
-#ifndef RTW_SORTED_CORNELL_BS
-#define RTW_SORTED_CORNELL_BS 512
-#endif
-    constexpr int BS = RTW_SORTED_MB2_COND ? RTW_SORTED_BVH_BS : (F == kVariants[0] ? RTW_SORTED_CORNELL_BS : kSBlock);
+    constexpr int cfg = (F == kVariants[0]) ? RTW_CFG_CORNELL : ((F & F_BVH) ? (SM < 2 ? RTW_CFG_BVH_UNSTAGED : RTW_CFG_BVH_STAGED) : RTW_CFG_TEX);
+    constexpr int BS = cfg / 1000, PT = cfg / 10 % 100, MB = cfg % 10;
+    static_assert(BS % 32 == 0 && BS <= 1024 && pool_slots(PT) <= 2048, "block size / pool out of range");
     // `smem` (staged bytes + traversal stacks) was planned for kSBlock threads: the stacks scale with the block size
     const size_t staged = SM == 2 ? sc.all_bytes : (SM == 1 ? sc.hot_bytes : 0);
     smem = staged + (smem - staged) / kSBlock * BS;
@@ -337,9 +331,6 @@ cudaError_t launch_sorted_t(const DevScene& sc, const DevRenderParams& rp, float
     const size_t bytes = pool_off + sorted_pool_bytes(PT);
     cudaError_t e = cudaFuncSetAttribute(render_sorted<F, SM, PT, MB, BS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
     if (e != cudaSuccess) return e;
-#ifdef RTW_SORTED_CARVEOUT
-    if (RTW_SORTED_MB2_COND) cudaFuncSetAttribute(render_sorted<F, SM, PT, MB, BS>, cudaFuncAttributePreferredSharedMemoryCarveout, RTW_SORTED_CARVEOUT);
-#endif
     if (getenv("RTW_DEBUG_TREES")) {
         int nb = 0;
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, render_sorted<F, SM, PT, MB, BS>, BS, bytes);
