@@ -174,9 +174,12 @@ def run_ours(args) -> None:
         if world == 1 and args.gpus > 1:
             raise SystemExit("launch with torchrun --nproc-per-node N for --gpus N")
     torch.cuda.set_device(local)
+    # stdout must carry ONE JSON line: NCCL prints its version banner to the process's stdout (C stdio) at communicator set-up,
+    # so file descriptor 1 points at stderr for the whole run and the line is written to the saved descriptor at the end
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     if world > 1:
-        # NCCL prints its version banner (NCCL_DEBUG=VERSION/INFO on the box) to stdout by default: keep stdout = ONE JSON line
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     lib = _lib.load()  # fails loudly when the CUDA library is missing
 
@@ -322,7 +325,8 @@ def run_ours(args) -> None:
     if cpu:
         line["cpu_baseline"] = cpu
         line["speedup_vs_cpu_reference"] = {"device": value / cpu["value"], "e2e": e2e["value"] / cpu["value"]}
-    print(json.dumps(line))
+    sys.stdout.flush()
+    os.write(json_fd, (json.dumps(line) + "\n").encode())
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
