@@ -92,7 +92,7 @@ RTW_DEV void bvh_hit(const SceneView& sv, int root, const RayK& rk, float time, 
     }
 }
 
-// Which kernel variants walk the 4-wide tree.  Measured on B200 (tools/ab_bvh4.sh): random_balls_scene 2.27 -> 2.49
+// Which kernel variants walk the 4-wide tree.  Measured on B200 (tools/ab_libs.sh): random_balls_scene 2.27 -> 2.49
 // Gpaths/s (node visits x0.57), but the all-features kernels lose 4-7 % (Book-2 final 0.452 -> 0.422, and Cornell smoke,
 // which has no tree at all, 3.96 -> 3.80: those kernels are bound by instruction fetch and by the longest lane of a warp,
 // not by the number of node fetches), so they keep the binary tree.
