@@ -5,7 +5,7 @@
 // shared memory instead of registers, and the warps of a block exchange paths through per-class queues so that a
 // warp always shades 32 paths of ONE material class and then traces their 32 new rays:
 //
-//   block  = 256 or 512 threads (per variant, launch_sorted_t), one 16x16 pixel tile, one pool of (pixel, sample) items like the
+//   block  = 256, 512 or 768 threads (per variant class, launch_sorted_t), one 16x16 pixel tile, one pool of (pixel, sample) items like the
 //            warp pool of kernels.cu
 //   slots  = kSPool path slots in shared memory, 64 B each: (o, t) (d, time) (beta, prim) (item, pixel, sample, bounce)
 //   queues = one ring of slot ids per class in shared memory {lambertian, dielectric, metal, isotropic, terminal
