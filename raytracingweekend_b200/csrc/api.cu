@@ -17,17 +17,47 @@ using namespace rtw;
 
 namespace {
 
+// Device memory comes from the device's default stream-ordered pool with an unlimited release threshold: a host that
+// creates, renders and destroys a scene per frame (bench.py's end-to-end step, the adapter's render()) gets the same
+// memory back in microseconds instead of paying cudaMalloc / cudaFree (~1 ms each, device-wide synchronisation) every
+// time.  The pool keeps what was freed (at most the peak use) until the process ends.  Allocation is followed by a
+// synchronisation of the legacy stream, so the pointer is valid on every stream, as with cudaMalloc.
+cudaError_t dev_alloc(void** p, size_t bytes) {
+    static bool configured[64] = {};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev >= 0 && dev < 64 && !configured[dev]) {
+        cudaMemPool_t pool;
+        if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+            unsigned long long keep = ~0ull;
+            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        }
+        cudaGetLastError();
+        configured[dev] = true;
+    }
+    if ((e = cudaMallocAsync(p, bytes, 0)) != cudaSuccess) return e;
+    return cudaStreamSynchronize(0);
+}
+// The caller has finished its renders (rtw_render_device_finish); like cudaFree, wait for the device before the memory
+// goes back to the pool.
+void dev_free(void* p) {
+    if (!p) return;
+    cudaDeviceSynchronize();
+    cudaFreeAsync(p, 0);
+}
+
 struct DevBuf {
     void* p = nullptr;
     template <typename T>
     cudaError_t upload(const std::vector<T>& v) {
         if (v.empty()) return cudaSuccess;
-        cudaError_t e = cudaMalloc(&p, v.size() * sizeof(T));
+        cudaError_t e = dev_alloc(&p, v.size() * sizeof(T));
         if (e != cudaSuccess) return e;
         return cudaMemcpy(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice);
     }
     void release() {
-        if (p) cudaFree(p);
+        dev_free(p);
         p = nullptr;
     }
 };
@@ -124,9 +154,9 @@ struct rtw_scene {
     void release() {
         blob.release();
         texels.release();
-        if (d_counter) cudaFree(d_counter);
-        if (scratch_accum) cudaFree(scratch_accum);
-        if (wf_scratch) cudaFree(wf_scratch);
+        dev_free(d_counter);
+        dev_free(scratch_accum);
+        dev_free(wf_scratch);
         if (wf_host_flag) cudaFreeHost(wf_host_flag);
         if (ev0) cudaEventDestroy(ev0);
         if (ev1) cudaEventDestroy(ev1);
@@ -164,8 +194,8 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
         cudaGetLastError();
         return nullptr;
     }
-    cudaDeviceProp prop;
-    if (!dry_run && ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess || prop.major != 10)) {
+    int cc_major = 0;  // one attribute, not cudaGetDeviceProperties (which takes ~1 ms and this runs once per scene)
+    if (!dry_run && ((e = cudaDeviceGetAttribute(&cc_major, cudaDevAttrComputeCapabilityMajor, device)) != cudaSuccess || cc_major != 10)) {
         set_error("scene_create: device is not compute capability 10.x (kernels are built for sm_100a only)");
         return nullptr;
     }
@@ -807,7 +837,7 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
     rtw_scene* s = new (std::nothrow) rtw_scene();
     if (!s) return nullptr;
     s->device = device;
-    cudaError_t err[] = {s->blob.upload(blob), s->texels.upload(texels), cudaMalloc(&s->d_counter, sizeof(unsigned long long)),
+    cudaError_t err[] = {s->blob.upload(blob), s->texels.upload(texels), dev_alloc((void**)&s->d_counter, sizeof(unsigned long long)),
                          cudaEventCreate(&s->ev0), cudaEventCreate(&s->ev1)};
     for (cudaError_t x : err)
         if (x != cudaSuccess) {
@@ -911,9 +941,9 @@ extern "C" int rtw_render_device(rtw_scene* s, const rtw_render_params* p, float
         want = (want + 255) & ~255ull;
         if (want < 256) want = 256;
         if ((uint32_t)want != s->wf_slots) {
-            if (s->wf_scratch) cudaFree(s->wf_scratch);
+            dev_free(s->wf_scratch);
             s->wf_scratch = nullptr, s->wf_slots = 0;
-            if ((e = cudaMalloc(&s->wf_scratch, wavefront_scratch_bytes((uint32_t)want))) != cudaSuccess) return cuda_fail(e, "cudaMalloc wavefront pool");
+            if ((e = dev_alloc((void**)&s->wf_scratch, wavefront_scratch_bytes((uint32_t)want))) != cudaSuccess) return cuda_fail(e, "cudaMalloc wavefront pool");
             s->wf_slots = (uint32_t)want;
         }
         if (!s->wf_host_flag && (e = cudaMallocHost((void**)&s->wf_host_flag, 16)) != cudaSuccess) return cuda_fail(e, "cudaMallocHost");
@@ -969,10 +999,10 @@ extern "C" int rtw_render(rtw_scene* s, const rtw_render_params* p, float* accum
     if (e != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
     size_t pixels = (size_t)p->nx * p->ny;
     if (pixels > s->scratch_pixels) {
-        if (s->scratch_accum) cudaFree(s->scratch_accum);
+        dev_free(s->scratch_accum);
         s->scratch_accum = nullptr;
         s->scratch_pixels = 0;
-        if ((e = cudaMalloc(&s->scratch_accum, pixels * 4 * sizeof(float))) != cudaSuccess) return cuda_fail(e, "cudaMalloc accum");
+        if ((e = dev_alloc((void**)&s->scratch_accum, pixels * 4 * sizeof(float))) != cudaSuccess) return cuda_fail(e, "cudaMalloc accum");
         s->scratch_pixels = pixels;
     }
     if (p->flags & RTW_FLAG_ACCUMULATE)
@@ -1010,14 +1040,14 @@ extern "C" int rtw_intersect_batch(rtw_scene* s, const rtw_ray* rays, rtw_hit* h
     rtw_ray* d_rays = nullptr;
     rtw_hit* d_hits = nullptr;
     int rc = RTW_OK;
-    if ((e = cudaMalloc(&d_rays, n * sizeof(rtw_ray))) != cudaSuccess || (e = cudaMalloc(&d_hits, n * sizeof(rtw_hit))) != cudaSuccess ||
+    if ((e = dev_alloc((void**)&d_rays, n * sizeof(rtw_ray))) != cudaSuccess || (e = dev_alloc((void**)&d_hits, n * sizeof(rtw_hit))) != cudaSuccess ||
         (e = cudaMemcpy(d_rays, rays, n * sizeof(rtw_ray), cudaMemcpyHostToDevice)) != cudaSuccess) {
         rc = cuda_fail(e, "intersect_batch buffers");
     } else if ((rc = rtw_intersect_batch_device(s, d_rays, d_hits, n, tmin, tmax, nullptr)) == RTW_OK) {
         if ((e = cudaMemcpy(hits, d_hits, n * sizeof(rtw_hit), cudaMemcpyDeviceToHost)) != cudaSuccess) rc = cuda_fail(e, "intersect_batch D2H");
     }
-    if (d_rays) cudaFree(d_rays);
-    if (d_hits) cudaFree(d_hits);
+    dev_free(d_rays);
+    dev_free(d_hits);
     return rc;
 }
 

@@ -72,7 +72,8 @@ inline Launch plan(const DevScene& sc, int block, bool exact = false) {
     size_t staged = l.stage == 2 ? sc.all_bytes : (l.stage == 1 ? sc.hot_bytes : 0);
     // exact needs computed at upload (api.cu push_need), + 1 entry of slack
     int entries = 1 + (exact ? sc.stack_exact : (bvh4_variant(l.variant) ? sc.bvh4_stack : sc.stack_render));
-    if (const char* extra = getenv("RTW_STACK_EXTRA")) entries += atoi(extra);  // diagnostics: cost of a deeper stack
+    static const int extra = [] { const char* v = getenv("RTW_STACK_EXTRA"); return v ? atoi(v) : 0; }();  // diagnostics: cost of a deeper stack
+    entries += extra;
     size_t stack = (l.variant & F_BVH) ? (size_t)entries * block * sizeof(int) : 0;
     l.smem = staged + stack;
     return l;

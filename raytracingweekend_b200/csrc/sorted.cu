@@ -331,7 +331,8 @@ cudaError_t launch_sorted_t(const DevScene& sc, const DevRenderParams& rp, float
     const size_t bytes = pool_off + sorted_pool_bytes(PT);
     cudaError_t e = cudaFuncSetAttribute(render_sorted<F, SM, PT, MB, BS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
     if (e != cudaSuccess) return e;
-    if (getenv("RTW_DEBUG_TREES")) {
+    static const bool debug = getenv("RTW_DEBUG_TREES") != nullptr;  // read once per process
+    if (debug) {
         int nb = 0;
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, render_sorted<F, SM, PT, MB, BS>, BS, bytes);
         fprintf(stderr, "rtw render_sorted<%u,%d,%d,%d,%d>: %zu bytes of shared memory per block (stack %zu), %d blocks/SM\n", F, SM, PT, MB, BS,
