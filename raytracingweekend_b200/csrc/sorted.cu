@@ -23,7 +23,7 @@
 // doubling the rings.
 //
 // Per-pixel sums are 64-bit fixed point (2^-24) in shared memory: integer adds commute, so the image stays
-// bit-reproducible although units run in a timing-dependent order.  Samples that are not finite or >= 8192 go to a
+// bit-reproducible although units run in a timing-dependent order.  Samples that are not finite or >= 2^30 go to a
 // float side accumulator (NaN / Inf propagate like in the reference).  HBM traffic is unchanged: one 16-byte
 // store per pixel per launch.
 #include <cstdio>
@@ -208,7 +208,10 @@ __global__ void __launch_bounds__(BS, MB) render_sorted(const __grid_constant__ 
 #pragma unroll
                     for (int ch = 0; ch < 3; ch++) {
                         if (v[ch] != 0.0f) {
-                            if (fabsf(v[ch]) < 8192.0f)
+                            // below 8192 a pixel's 2^23 samples cannot overflow the 64-bit sum; fireflies up to 2^30 take the
+                            // same (exact, commutative) integer path — it would take > 448 of them at 1e9 in ONE pixel of one
+                            // launch to wrap; only samples >= 2^30 or not finite go to the float side sum
+                            if (fabsf(v[ch]) < 1073741824.0f)
                                 atomicAdd(fx + ch * kSPix + pix, (unsigned long long)__float2ll_rn(v[ch] * 16777216.0f));
                             else
                                 atomicAdd(fl + ch * kSPix + pix, v[ch]);
