@@ -295,7 +295,10 @@ typedef struct rtw_render_stats {
  * rtw_render:        host buffer, synchronous (device->host copy included).
  * rtw_render_device: device buffer on the scene's device, asynchronous on `cuda_stream`
  *                    (a cudaStream_t passed as void*; NULL = legacy default stream);
- *                    stats->rays/kernel_ms are valid after rtw_render_device_finish. */
+ *                    stats->rays/kernel_ms are valid after rtw_render_device_finish.  ONE render in flight per
+ *                    rtw_scene (its ray counter and timing events live in the scene): a second rtw_render_device
+ *                    before rtw_render_device_finish returns RTW_ERR_INVALID.  With RTW_FLAG_WAVEFRONT the call is
+ *                    synchronous (the host polls the pool between chunks of iterations). */
 int rtw_render(rtw_scene* s, const rtw_render_params* p, float* accum_host_rgba, rtw_render_stats* stats);
 int rtw_render_device(rtw_scene* s, const rtw_render_params* p, float* accum_dev_rgba, void* cuda_stream);
 int rtw_render_device_finish(rtw_scene* s, rtw_render_stats* stats);
@@ -315,6 +318,35 @@ int rtw_intersect_batch(rtw_scene* s, const rtw_ray* rays_host, rtw_hit* hits_ho
                         float t_max);
 int rtw_intersect_batch_device(rtw_scene* s, const rtw_ray* rays_dev, rtw_hit* hits_dev, int64_t n, float t_min,
                                float t_max, void* cuda_stream);
+
+/* ------------------------------------------------------------------ 4. multi-GPU
+ * The reference has ONE process; its seam RayTracingWeekend.cpp:211-250 produces all samples of every pixel and :241-244
+ * tonemaps them.  Here GPU g of G renders the global sample indices [g*spp/G, (g+1)*spp/G) of every pixel (Philox
+ * streams are keyed by the global sample index, so shards are disjoint and their union is the 1-GPU render), the float4
+ * accumulators are summed onto the root with one ncclReduce over NVLink, and the root alone tonemaps and writes.
+ * One process (or thread) per GPU.  NCCL is bound at run time (dlopen libnccl.so.2; RTW_NCCL_LIB overrides). */
+#define RTW_COMM_ID_BYTES 128
+typedef struct rtw_comm rtw_comm;
+/* ncclGetUniqueId: call on ONE rank and hand the 128 bytes to the others (file, socket, MPI, torch.distributed ...). */
+int rtw_comm_unique_id(uint8_t id[RTW_COMM_ID_BYTES]);
+/* ncclCommInitRank on `device`; collective over all ranks.  NULL on error. */
+rtw_comm* rtw_comm_create(const uint8_t id[RTW_COMM_ID_BYTES], int rank, int world, int device);
+/* Wrap an ncclComm_t the host application already owns (not destroyed by rtw_comm_destroy). */
+rtw_comm* rtw_comm_adopt(void* nccl_comm, int rank, int world, int device);
+void rtw_comm_destroy(rtw_comm* c);
+int rtw_comm_rank(const rtw_comm* c);
+int rtw_comm_world(const rtw_comm* c);
+/* Sample range of `rank`: [rank*spp/world, (rank+1)*spp/world); the ranges tile [0, spp) exactly. */
+int rtw_shard_range(int spp, int rank, int world, int* spp_begin, int* spp_count);
+/* In-place sum of the per-rank accumulators (nx*ny float4, device memory) onto `root`, asynchronous on `cuda_stream`;
+ * the w channel carries sample counts, so the root's buffer is again (sum r, sum g, sum b, samples).  c == NULL or one
+ * rank: no-op. */
+int rtw_reduce_accumulators(rtw_comm* c, float* accum_dev_rgba, int nx, int ny, int root, void* cuda_stream);
+/* The whole multi-GPU step: `whole` names ALL samples; this rank renders its shard, the sums are reduced onto `root`,
+ * which alone receives the image in host memory (accum_host_root may be NULL on the other ranks).  Synchronous.
+ * stats = this rank's shard. */
+int rtw_render_sharded(rtw_scene* s, rtw_comm* c, const rtw_render_params* whole, int root, float* accum_host_root,
+                       rtw_render_stats* stats);
 
 /* ------------------------------------------------------------------ host-side output (rank 0)
  * RayTracingWeekend.cpp:241-244: mean, sqrt gamma, min(.,1) -> canvas (3 doubles per pixel). */

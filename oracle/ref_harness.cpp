@@ -66,6 +66,8 @@ std::unique_ptr<scene> make_scene(const std::string& name, double aspect) {
     if (name == "random_balls_scene") return std::unique_ptr<scene>(new random_balls_scene(aspect));
     if (name == "cornell_box_scene") return std::unique_ptr<scene>(new cornell_box_scene(aspect));
     if (name == "cornell_box_aluminum") return std::unique_ptr<scene>(new cornell_box_aluminum_scene(aspect));
+    if (name == "cornell_two_boxes") return std::unique_ptr<scene>(new cornell_no_glass_scene(aspect, false));
+    if (name == "cornell_aluminum_box") return std::unique_ptr<scene>(new cornell_no_glass_scene(aspect, true));
     if (name == "cornell_smoke_scene") return std::unique_ptr<scene>(new cornell_smoke_scene(aspect));
     if (name == "checker_spheres_scene") return std::unique_ptr<scene>(new checker_spheres_scene(aspect));
     if (name == "two_perlin_spheres_earth" && g_earth)

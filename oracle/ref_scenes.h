@@ -37,6 +37,42 @@ public:
     }
 };
 
+// Scene/scene.h:176-249 with the `#if 1` at :219-225 switched OFF: the short box (:212-217) stays, no glass sphere, and the
+// area light alone is in `lights` ("cornell_two_boxes", the reference's CornellBox.png strip); with `aluminum` also the
+// `#if 0` at :228-231 ON: the scene of Sampling/12.2.png ("cornell_aluminum_box").  Twin of scenes.cpp cornell_box_scene.
+class cornell_no_glass_scene : public scene {
+public:
+    cornell_no_glass_scene(double aspect, bool aluminum_tall_box) : scene() {
+        std::shared_ptr<texture> red_tex = std::make_shared<constant_texture>(vec3(0.65f, 0.05f, 0.05f));
+        auto red = std::make_shared<lambertian>(red_tex);
+        std::shared_ptr<texture> white_tex = std::make_shared<constant_texture>(vec3(0.73f, 0.73f, 0.73f));
+        auto white = std::make_shared<lambertian>(white_tex);
+        std::shared_ptr<texture> green_tex = std::make_shared<constant_texture>(vec3(0.12f, 0.45f, 0.15f));
+        auto green = std::make_shared<lambertian>(green_tex);
+        std::shared_ptr<texture> light_tex = std::make_shared<constant_texture>(vec3(15.0, 15.0, 15.0));
+        auto light = std::make_shared<diffuse_light>(light_tex);
+        std::vector<std::shared_ptr<hittable>> objects;
+        objects.push_back(std::make_shared<xz_rect>(213.0, 343.0, 227.0, 332.0, 554.0, light));
+        lights->objects.push_back(objects.back());
+        objects.push_back(std::make_shared<flip_normals>(std::make_shared<yz_rect>(0.0, 555.0, 0.0, 555.0, 555.0, green)));
+        objects.push_back(std::make_shared<yz_rect>(0.0, 555.0, 0.0, 555.0, 0.0, red));
+        objects.push_back(std::make_shared<flip_normals>(std::make_shared<xz_rect>(0.0, 555.0, 0.0, 555.0, 555.0, white)));
+        objects.push_back(std::make_shared<xz_rect>(0.0, 555.0, 0.0, 555.0, 0.0, white));
+        objects.push_back(std::make_shared<flip_normals>(std::make_shared<xy_rect>(0.0, 555.0, 0.0, 555.0, 555.0, white)));
+        objects.push_back(std::make_shared<translate>(
+            std::make_shared<rotate_y>(std::make_shared<box>(vec3(0.0, 0.0, 0.0), vec3(165.0, 165.0, 165.0), white), -18.0),
+            vec3(130.0, 0.0, 65.0)));
+        std::shared_ptr<material> tall = white;
+        if (aluminum_tall_box) tall = std::make_shared<metal>(vec3(0.8, 0.85, 0.88), 0.0);
+        objects.push_back(std::make_shared<translate>(
+            std::make_shared<rotate_y>(std::make_shared<box>(vec3(0.0, 0.0, 0.0), vec3(165.0, 330.0, 165.0), tall), 15.0),
+            vec3(265.0, 0.0, 295.0)));
+        this->world = hittable_list(objects);
+        this->cam = camera(vec3(278.0, 278.0, -800.0), vec3(278.0, 278.0, 0.0), vec3(0.0, 1.0, 0.0), 40.0, aspect, 0.0, 10.0, 0.0, 1.0);
+        this->background_type = BackgroundType::Black;
+    }
+};
+
 // cfg2: Book-2 Perlin spheres + earth image_texture sphere.
 class two_perlin_spheres_earth_scene : public scene {
 public:

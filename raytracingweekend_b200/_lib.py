@@ -14,6 +14,7 @@ RTW_FLAG_WAVEFRONT = 1
 RTW_FLAG_AUTO = 8
 RTW_FLAG_ACCUMULATE = 2
 RTW_FLAG_DEBUG_RAY = 4
+RTW_COMM_ID_BYTES = 128
 
 
 class FlatCamera(C.Structure):
@@ -138,6 +139,15 @@ SIGNATURES = {
     "rtw_write_ppm_binary": (C.c_int, [C.c_char_p, _P, C.c_int, C.c_int]),
     "rtw_write_png": (C.c_int, [C.c_char_p, _P, C.c_int, C.c_int]),
     "rtw_decode_jpeg": (C.c_int, [_P, C.c_size_t, _P, C.c_size_t, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "rtw_comm_unique_id": (C.c_int, [_P]),
+    "rtw_comm_create": (_P, [_P, C.c_int, C.c_int, C.c_int]),
+    "rtw_comm_adopt": (_P, [_P, C.c_int, C.c_int, C.c_int]),
+    "rtw_comm_destroy": (None, [_P]),
+    "rtw_comm_rank": (C.c_int, [_P]),
+    "rtw_comm_world": (C.c_int, [_P]),
+    "rtw_shard_range": (C.c_int, [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "rtw_reduce_accumulators": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, _P]),
+    "rtw_render_sharded": (C.c_int, [_P, _P, C.POINTER(RenderParams), C.c_int, _P, C.POINTER(RenderStats)]),
     "rtw_device_count": (C.c_int, []),
     "rtw_measure_fp32_peak": (C.c_int, [C.c_int, C.POINTER(C.c_double)]),
 }

@@ -19,7 +19,8 @@ from ._lib import RenderParams, RenderStats, check
 GOLDEN_EARTH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests", "golden", "earth_256x256_rgb8.bin")
 
 SCENE_NAMES = ("light_sample", "dielectric_scene", "random_balls_scene", "cornell_box_scene", "cornell_box_aluminum",
-               "two_perlin_spheres_earth", "book2_final_scene", "cornell_smoke_scene", "checker_spheres_scene")
+               "two_perlin_spheres_earth", "book2_final_scene", "cornell_smoke_scene", "checker_spheres_scene", "cornell_two_boxes",
+               "cornell_aluminum_box")
 
 
 def _d3(v: Sequence[float]):
@@ -188,6 +189,20 @@ class Scene:
         """Asynchronous render into a device buffer (e.g. torch tensor .data_ptr()) on `stream`."""
         p = self._params(nx, ny, spp, spp_begin, max_depth, seed, flags)
         check(self._l.rtw_render_device(self._s, C.byref(p), C.c_void_p(accum_ptr), C.c_void_p(stream)), "rtw_render_device")
+
+    def render_sharded(self, comm, nx, ny, spp, spp_begin=0, max_depth=100, seed=0, flags=0, root=0,
+                       out: Optional[np.ndarray] = None):
+        """rtw_render_sharded: this rank renders its share of the `spp` samples, the sums are reduced onto `root`
+        (ncclReduce inside the library), and the root alone gets the image.  `comm` is a dist.Communicator (or None for a
+        single rank).  Returns (accum on the root / None elsewhere, stats of the local shard)."""
+        rank = comm.rank if comm is not None else 0
+        acc = None
+        if rank == root:
+            acc = out if out is not None else np.empty((ny, nx, 4), dtype=np.float32)
+        p, st = self._params(nx, ny, spp, spp_begin, max_depth, seed, flags), RenderStats()
+        check(self._l.rtw_render_sharded(self._s, comm.handle if comm is not None else None, C.byref(p), root,
+                                         acc.ctypes.data_as(C.c_void_p) if acc is not None else None, C.byref(st)), "rtw_render_sharded")
+        return acc, _stats(st)
 
     def finish(self) -> dict:
         st = RenderStats()

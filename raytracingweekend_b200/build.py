@@ -82,5 +82,11 @@ def build(force: bool = False, verbose: bool = False, extra: list[str] | None = 
     return full_so
 
 
+def build_count(force: bool = False) -> str:
+    """Diagnostics twin of the library with device-side traversal event counters (tools/count_tree_events.py; bench.py uses
+    it for roofline.kernel_tree).  Never loaded by the product path."""
+    return build(force=force, extra=["-DRTW_COUNT_EVENTS"], tag="_count")
+
+
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

@@ -5,10 +5,14 @@
 #include <cmath>
 #include <functional>
 #include <limits>
+#include <mutex>
 #include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
+
+#include <dlfcn.h>
+#include <nccl.h>  // types only: the library is bound with dlopen (multi-GPU section at the end)
 
 #include "flat.hpp"
 #include "kernels.hpp"
@@ -17,33 +21,45 @@ using namespace rtw;
 
 namespace {
 
-// Device memory comes from the device's default stream-ordered pool with an unlimited release threshold: a host that
-// creates, renders and destroys a scene per frame (bench.py's end-to-end step, the adapter's render()) gets the same
+// Device memory comes from a PRIVATE stream-ordered pool per device (created once, release threshold unlimited): a host
+// that creates, renders and destroys a scene per frame (bench.py's end-to-end step, the adapter's render()) gets the same
 // memory back in microseconds instead of paying cudaMalloc / cudaFree (~1 ms each, device-wide synchronisation) every
-// time.  The pool keeps what was freed (at most the peak use) until the process ends.  Allocation is followed by a
-// synchronisation of the legacy stream, so the pointer is valid on every stream, as with cudaMalloc.
+// time, and the host application's default pool keeps its own attributes.  The pool keeps what was freed (at most the peak
+// use) until the process ends.  Allocation is followed by a synchronisation of the legacy stream, so the pointer is valid
+// on every stream, as with cudaMalloc.
 cudaError_t dev_alloc(void** p, size_t bytes) {
-    static bool configured[64] = {};
+    static std::mutex mu;
+    static cudaMemPool_t pools[64] = {};
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return e;
-    if (dev >= 0 && dev < 64 && !configured[dev]) {
-        cudaMemPool_t pool;
-        if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    cudaMemPool_t pool;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        if (!pools[dev]) {
+            cudaMemPoolProps props{};
+            props.allocType = cudaMemAllocationTypePinned;
+            props.handleTypes = cudaMemHandleTypeNone;
+            props.location.type = cudaMemLocationTypeDevice;
+            props.location.id = dev;
+            if ((e = cudaMemPoolCreate(&pools[dev], &props)) != cudaSuccess) {
+                pools[dev] = nullptr;
+                return e;
+            }
             unsigned long long keep = ~0ull;
-            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+            cudaMemPoolSetAttribute(pools[dev], cudaMemPoolAttrReleaseThreshold, &keep);
         }
-        cudaGetLastError();
-        configured[dev] = true;
+        pool = pools[dev];
     }
-    if ((e = cudaMallocAsync(p, bytes, 0)) != cudaSuccess) return e;
+    if ((e = cudaMallocFromPoolAsync(p, bytes, pool, 0)) != cudaSuccess) return e;
     return cudaStreamSynchronize(0);
 }
-// The caller has finished its renders (rtw_render_device_finish); like cudaFree, wait for the device before the memory
-// goes back to the pool.
+// Stream-ordered free on the legacy stream.  The CALLER guarantees that no work on another stream still uses `p`:
+// rtw_scene::release waits for the scene's last render (one event, not a device-wide synchronisation per buffer), the
+// host-buffer entry points are synchronous.
 void dev_free(void* p) {
     if (!p) return;
-    cudaDeviceSynchronize();
     cudaFreeAsync(p, 0);
 }
 
@@ -151,7 +167,11 @@ struct rtw_scene {
     void* wf_scratch = nullptr;  // wavefront path pool + queues (lazy)
     uint32_t wf_slots = 0;
     unsigned long long* wf_host_flag = nullptr;  // pinned
+    bool rendered = false;  // ev1 was recorded at least once
     void release() {
+        // one wait for the scene's last render instead of a device-wide synchronisation per buffer: every other use of
+        // these buffers (upload, intersect_batch, host-buffer renders) is synchronous
+        if (rendered && ev1) cudaEventSynchronize(ev1);
         blob.release();
         texels.release();
         dev_free(d_counter);
@@ -910,6 +930,10 @@ extern "C" int rtw_render_device(rtw_scene* s, const rtw_render_params* p, float
         set_error("render: null accumulator");
         return RTW_ERR_INVALID;
     }
+    if (s->pending) {  // the ray counter and the two timing events live in the scene: one render in flight per rtw_scene
+        set_error("render: the previous rtw_render_device of this scene has not been finished (rtw_render_device_finish)");
+        return RTW_ERR_INVALID;
+    }
     cudaStream_t st = (cudaStream_t)cuda_stream;
     cudaError_t e = cudaSetDevice(s->device);
     if (e != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
@@ -958,6 +982,7 @@ extern "C" int rtw_render_device(rtw_scene* s, const rtw_render_params* p, float
         if (e != cudaSuccess) return cuda_fail(e, "render launch");
     }
     if ((e = cudaEventRecord(s->ev1, st)) != cudaSuccess) return cuda_fail(e, "event");
+    s->rendered = true;
     s->pending = true;
     s->pending_params = *p;
     s->pending_launches = launches;
@@ -1059,5 +1084,198 @@ extern "C" int rtw_measure_fp32_peak(int device, double* tflops) {
     cudaError_t e = cudaSetDevice(device);
     if (e != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
     if ((e = measure_fp32_peak(tflops)) != cudaSuccess) return cuda_fail(e, "fp32 peak probe");
+    return RTW_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ multi-GPU
+// Samples-per-pixel sharding + ONE sum-reduce of the float4 accumulators onto the root.  The seam is still
+// RayTracingWeekend.cpp:211-250: the root ends up with the radiance sums of ALL samples and alone applies :241-244.
+// NCCL is bound at run time (dlopen of libnccl.so.2: the copy the host process already loaded, e.g. torch's, else the
+// system one), so the library carries no link-time dependency and single-GPU users never touch it.
+namespace {
+
+struct NcclApi {
+    void* handle = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*Reduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    const char* (*GetErrorString)(ncclResult_t) = nullptr;
+    ncclResult_t (*GetVersion)(int*) = nullptr;
+};
+
+const NcclApi* nccl_api() {
+    static NcclApi api;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        const char* names[] = {getenv("RTW_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
+        for (const char* n : names) {
+            if (!n) continue;
+            if ((api.handle = dlopen(n, RTLD_NOW | RTLD_GLOBAL)) != nullptr) break;
+        }
+        if (!api.handle) return;
+        api.GetUniqueId = (decltype(api.GetUniqueId))dlsym(api.handle, "ncclGetUniqueId");
+        api.CommInitRank = (decltype(api.CommInitRank))dlsym(api.handle, "ncclCommInitRank");
+        api.CommDestroy = (decltype(api.CommDestroy))dlsym(api.handle, "ncclCommDestroy");
+        api.Reduce = (decltype(api.Reduce))dlsym(api.handle, "ncclReduce");
+        api.GetErrorString = (decltype(api.GetErrorString))dlsym(api.handle, "ncclGetErrorString");
+        api.GetVersion = (decltype(api.GetVersion))dlsym(api.handle, "ncclGetVersion");
+        if (!api.GetUniqueId || !api.CommInitRank || !api.CommDestroy || !api.Reduce || !api.GetErrorString) api.handle = nullptr;
+    });
+    if (!api.handle) {
+        set_error("multi-GPU: libnccl.so.2 not found (set RTW_NCCL_LIB to its path)");
+        return nullptr;
+    }
+    return &api;
+}
+
+int nccl_fail(const NcclApi* a, ncclResult_t r, const char* what) {
+    set_error(std::string(what) + ": " + a->GetErrorString(r));
+    return RTW_ERR_CUDA;
+}
+
+}  // namespace
+
+struct rtw_comm {
+    ncclComm_t comm = nullptr;
+    int rank = 0, world = 1, device = 0;
+    bool owned = true;
+};
+
+static_assert(sizeof(ncclUniqueId) == RTW_COMM_ID_BYTES, "rtw_comm id size");
+
+extern "C" int rtw_comm_unique_id(uint8_t* id) {
+    const NcclApi* a = nccl_api();
+    if (!a) return RTW_ERR_CUDA;
+    if (!id) {
+        set_error("comm_unique_id: null");
+        return RTW_ERR_INVALID;
+    }
+    ncclUniqueId u;
+    ncclResult_t r = a->GetUniqueId(&u);
+    if (r != ncclSuccess) return nccl_fail(a, r, "ncclGetUniqueId");
+    memcpy(id, &u, sizeof u);
+    return RTW_OK;
+}
+
+extern "C" rtw_comm* rtw_comm_create(const uint8_t* id, int rank, int world, int device) {
+    const NcclApi* a = nccl_api();
+    if (!a) return nullptr;
+    if (!id || world < 1 || rank < 0 || rank >= world) {
+        set_error("comm_create: bad id / rank / world");
+        return nullptr;
+    }
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) {
+        cuda_fail(e, "cudaSetDevice");
+        return nullptr;
+    }
+    ncclUniqueId u;
+    memcpy(&u, id, sizeof u);
+    rtw_comm* c = new rtw_comm();
+    c->rank = rank, c->world = world, c->device = device;
+    ncclResult_t r = a->CommInitRank(&c->comm, world, u, rank);
+    if (r != ncclSuccess) {
+        nccl_fail(a, r, "ncclCommInitRank");
+        delete c;
+        return nullptr;
+    }
+    return c;
+}
+
+extern "C" rtw_comm* rtw_comm_adopt(void* nccl_comm, int rank, int world, int device) {
+    if (!nccl_api()) return nullptr;
+    if (!nccl_comm || world < 1 || rank < 0 || rank >= world) {
+        set_error("comm_adopt: bad communicator / rank / world");
+        return nullptr;
+    }
+    rtw_comm* c = new rtw_comm();
+    c->comm = (ncclComm_t)nccl_comm, c->rank = rank, c->world = world, c->device = device, c->owned = false;
+    return c;
+}
+
+extern "C" void rtw_comm_destroy(rtw_comm* c) {
+    if (!c) return;
+    const NcclApi* a = nccl_api();
+    if (a && c->owned && c->comm) {
+        cudaSetDevice(c->device);
+        a->CommDestroy(c->comm);
+    }
+    delete c;
+}
+
+extern "C" int rtw_comm_rank(const rtw_comm* c) { return c ? c->rank : 0; }
+extern "C" int rtw_comm_world(const rtw_comm* c) { return c ? c->world : 1; }
+
+// [rank*spp/world, (rank+1)*spp/world): the ranges tile [0, spp) exactly; Philox streams are keyed by the GLOBAL sample index
+extern "C" int rtw_shard_range(int spp, int rank, int world, int* spp_begin, int* spp_count) {
+    if (spp < 0 || world < 1 || rank < 0 || rank >= world || !spp_begin || !spp_count) {
+        set_error("shard_range: bad arguments");
+        return RTW_ERR_INVALID;
+    }
+    const long long lo = (long long)rank * spp / world, hi = (long long)(rank + 1) * spp / world;
+    *spp_begin = (int)lo, *spp_count = (int)(hi - lo);
+    return RTW_OK;
+}
+
+extern "C" int rtw_reduce_accumulators(rtw_comm* c, float* accum_dev, int nx, int ny, int root, void* cuda_stream) {
+    if (!c || c->world == 1) return RTW_OK;  // one rank: the accumulator is already the sum
+    const NcclApi* a = nccl_api();
+    if (!a) return RTW_ERR_CUDA;
+    if (!accum_dev || nx <= 0 || ny <= 0 || root < 0 || root >= c->world) {
+        set_error("reduce_accumulators: bad arguments");
+        return RTW_ERR_INVALID;
+    }
+    cudaError_t e = cudaSetDevice(c->device);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
+    // in place: the w channel carries sample counts, so the reduced buffer is again (sum r, sum g, sum b, samples)
+    ncclResult_t r = a->Reduce(accum_dev, accum_dev, (size_t)4 * nx * ny, ncclFloat32, ncclSum, root, c->comm, (cudaStream_t)cuda_stream);
+    if (r != ncclSuccess) return nccl_fail(a, r, "ncclReduce");
+    return RTW_OK;
+}
+
+// The whole multi-GPU step behind one call: `whole` describes ALL samples [spp_begin, spp_begin + spp_count); this rank
+// renders its share of them, the accumulators are summed onto `root`, and the root alone receives the image
+// (accum_host_root may be NULL elsewhere).  stats = this rank's shard.
+extern "C" int rtw_render_sharded(rtw_scene* s, rtw_comm* c, const rtw_render_params* whole, int root, float* accum_host_root,
+                                  rtw_render_stats* stats) {
+    int rc = check_params(s, whole);
+    if (rc != RTW_OK) return rc;
+    const int rank = c ? c->rank : 0, world = c ? c->world : 1;
+    if (root < 0 || root >= world || (rank == root && !accum_host_root)) {
+        set_error("render_sharded: bad root / null image on the root");
+        return RTW_ERR_INVALID;
+    }
+    if (whole->flags & RTW_FLAG_ACCUMULATE) {
+        set_error("render_sharded: RTW_FLAG_ACCUMULATE is not supported here (accumulate on the root after the call)");
+        return RTW_ERR_INVALID;
+    }
+    cudaError_t e = cudaSetDevice(s->device);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
+    const size_t pixels = (size_t)whole->nx * whole->ny;
+    if (pixels > s->scratch_pixels) {
+        dev_free(s->scratch_accum);
+        s->scratch_accum = nullptr, s->scratch_pixels = 0;
+        if ((e = dev_alloc((void**)&s->scratch_accum, pixels * 16)) != cudaSuccess) return cuda_fail(e, "cudaMalloc accum");
+        s->scratch_pixels = pixels;
+    }
+    rtw_render_params p = *whole;
+    int b = 0, n = 0;
+    rtw_shard_range(whole->spp_count, rank, world, &b, &n);
+    p.spp_begin = whole->spp_begin + b, p.spp_count = n;
+    if (stats) memset(stats, 0, sizeof *stats);
+    if (n > 0) {
+        if ((rc = rtw_render_device(s, &p, s->scratch_accum, nullptr)) != RTW_OK) return rc;
+    } else if ((e = cudaMemsetAsync(s->scratch_accum, 0, pixels * 16, nullptr)) != cudaSuccess) {  // more ranks than samples
+        return cuda_fail(e, "memset");
+    }
+    // same stream: the reduce starts when the kernel ends; the stats are read after both are queued
+    if ((rc = rtw_reduce_accumulators(c, s->scratch_accum, whole->nx, whole->ny, root, nullptr)) != RTW_OK) return rc;
+    if (n > 0 && (rc = rtw_render_device_finish(s, stats)) != RTW_OK) return rc;
+    if (rank == root) {
+        if ((e = cudaMemcpy(accum_host_root, s->scratch_accum, pixels * 16, cudaMemcpyDeviceToHost)) != cudaSuccess) return cuda_fail(e, "D2H accum");
+    } else if ((e = cudaStreamSynchronize(nullptr)) != cudaSuccess) {
+        return cuda_fail(e, "reduce");
+    }
     return RTW_OK;
 }

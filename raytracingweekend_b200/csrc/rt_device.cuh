@@ -12,6 +12,16 @@ namespace rtw {
 
 #define RTW_DEV __device__ __forceinline__
 
+// Diagnostics build only (-DRTW_COUNT_EVENTS, librtw_b200_count.so): counts the traversal events the render kernel's own
+// acceleration structures cost, for the algorithmic-flop figure bench.py reports beside the reference-math count.
+#ifdef RTW_COUNT_EVENTS
+enum { EVC_AABB = 0, EVC_SPHERE_TEST, EVC_SPHERE_ROOT, EVC_MOVING, EVC_RECT, EVC_BOX, EVC_XF, EVC_N };
+static __device__ unsigned long long g_evc[8];
+#define RTW_EV(k, n) atomicAdd(&g_evc[k], (unsigned long long)(n))
+#else
+#define RTW_EV(k, n) ((void)0)
+#endif
+
 // ------------------------------------------------------------------------------------------------ vec3
 struct V3 {
     float x, y, z;
@@ -206,7 +216,9 @@ RTW_DEV bool sphere_roots(V3 oc, V3 d, float a, float inv_a, float radius, float
     V3 l = mk(fmaf(-ba, d.x, oc.x), fmaf(-ba, d.y, oc.y), fmaf(-ba, d.z, oc.z));
     float r2 = radius * radius;
     float disc = a * (r2 - dot(l, l));  // == b*b - a*c (sphere.h:53)
+    RTW_EV(EVC_SPHERE_TEST, 1);
     if (!(disc > 0.0f)) return false;
+    RTW_EV(EVC_SPHERE_ROOT, 1);
     float sq = sqrtf(disc);
     float c = dot(oc, oc) - r2;
     // q = -b - sign(b) sqrt(disc) never cancels; the roots are q/a and c/q
@@ -227,7 +239,9 @@ RTW_DEV bool sphere_roots_f64(const SceneView& sv, uint32_t pd_off, V3 o, V3 d, 
     double b = ocx * dx + ocy * dy + ocz * dz;
     double c = ocx * ocx + ocy * ocy + ocz * ocz - rad * rad;
     double disc = b * b - a * c;
+    RTW_EV(EVC_SPHERE_TEST, 1);
     if (!(disc > 0.0)) return false;
+    RTW_EV(EVC_SPHERE_ROOT, 1);
     // FP64 only where FP32 cancels (b*b - a*c and -b -+ sq for |r| >= 100); the division by a = d.d is the ray's FP32
     // reciprocal (2 ulp), which keeps two inlined FP64 divisions out of every copy of the sphere loop
     double sq = sqrt(disc);
@@ -253,6 +267,7 @@ RTW_DEV void rect_update(float4 ra, float k, int id, float on, float inv_n, floa
                          float& t_best, int& prim_best) {
     float t = (k - on) * inv_n;
     float a = fmaf(t, da, oa), b = fmaf(t, db, ob);
+    RTW_EV(EVC_RECT, 1);
     // two independent 3-deep predicate chains (t range + first axis | second axis) joined at the end: one more
     // instruction than a single 6-deep chain, half the dependent latency
     asm("{\n\t.reg .pred p, q;\n\t"
@@ -335,6 +350,7 @@ RTW_DEV RayK make_rayk(V3 o, V3 d) {
 // Ray constants in the object space of a translate/rotate_y chain: y is untouched by rotate_y, so 1/d.y carries over.
 RTW_DEV RayK xf_rayk(const DevXf& x, const RayK& w) {
     RayK k;
+    RTW_EV(EVC_XF, 1);
     xf_ray(x, w.o, w.d, k.o, k.d);
     k.inv = mk(rcp_fast(k.d.x), w.inv.y, rcp_fast(k.d.z));
     k.a = dot(k.d, k.d);
@@ -369,6 +385,7 @@ RTW_DEV float4 hot4_abs(const SceneView& sv, uint32_t addr) {
 // exit face; t = (k - o_n) * inv_n is the expression of rect_update, so the winner's t is bit-identical.  The rect ids are
 // id0 + {0: z = hi, 1: z = lo, 2: y = hi, 3: y = lo, 4: x = hi, 5: x = lo} (builder.cpp K_BOX).
 RTW_DEV void box_update(float4 lo, float4 hi, const RayK& k, float tmin, float& t_best, int& prim_best) {
+    RTW_EV(EVC_BOX, 1);
     const float tx0 = (lo.x - k.o.x) * k.inv.x, tx1 = (hi.x - k.o.x) * k.inv.x;
     const float ty0 = (lo.y - k.o.y) * k.inv.y, ty1 = (hi.y - k.o.y) * k.inv.y;
     const float tz0 = (lo.z - k.o.z) * k.inv.z, tz1 = (hi.z - k.o.z) * k.inv.z;
@@ -429,6 +446,7 @@ RTW_DEV void test_group_kinds(const SceneView& sv, float4 g0, float4 g1, const R
             float4 ra = hot4_abs<SM>(sv, r), rb = hot4_abs<SM>(sv, r + 16);
             // sphere.h:22-25 folded to c' + time*delta on the host
             V3 c = madd(mk(ra.x, ra.y, ra.z), time, mk(rb.x, rb.y, rb.z));
+            RTW_EV(EVC_MOVING, 1);
             float t0, t1, t;
             if (sphere_roots(k.o - c, k.d, k.a, k.inv_a, ra.w, t0, t1) && sphere_pick(t0, t1, tmin, t_best, t)) {
                 t_best = t;

@@ -47,6 +47,7 @@ RTW_DEV void bvh_hit(const SceneView& sv, int root, const RayK& rk, float time, 
             const float4 llo = hot4<SM>(sv, (uint32_t)ref), lhi = hot4<SM>(sv, (uint32_t)ref + 16);
             const float4 rlo = hot4<SM>(sv, (uint32_t)ref + 32), rhi = hot4<SM>(sv, (uint32_t)ref + 48);
             const float cull = (SHRINK && best_prim >= 0) ? fmaf(best, 4e-6f, best) : tmax;
+            RTW_EV(EVC_AABB, 2);
             float tl, tr;
             const bool hl = FAST_BOX ? slab_hit(llo, lhi, inv, oi, tmin, cull, tl) : aabb_hit(llo, lhi, o, inv, tmin, cull, tl);
             const bool hr = FAST_BOX ? slab_hit(rlo, rhi, inv, oi, tmin, cull, tr) : aabb_hit(rlo, rhi, o, inv, tmin, cull, tr);
@@ -130,6 +131,7 @@ RTW_DEV void bvh4_hit(const SceneView& sv, int root, const RayK& rk, float time,
 #endif
             const float4 rf = hot4<SM>(sv, a + 96u);
             const float cull = best_prim >= 0 ? fmaf(best, 4e-6f, best) : tmax;
+            RTW_EV(EVC_AABB, 4);
             float t0, t1, t2, t3;
 #if RTW_BVH4_OCTANT
 #define RTW_SLAB4(T, C)                                                                                                       \
@@ -241,6 +243,7 @@ RTW_UNIFIED_FN HitId bvh_hit_items(uint32_t items0, SceneView sv, RayK rk, float
             const float4 llo = hot4<SM>(sv, (uint32_t)ref), lhi = hot4<SM>(sv, (uint32_t)ref + 16);
             const float4 rlo = hot4<SM>(sv, (uint32_t)ref + 32), rhi = hot4<SM>(sv, (uint32_t)ref + 48);
             const float cull = best_prim >= 0 ? fmaf(best, 4e-6f, best) : tmax;
+            RTW_EV(EVC_AABB, 2);
             float tl, tr;
             const bool hl = aabb_hit(llo, lhi, lk.o, lk.inv, tmin, cull, tl);
             const bool hr = aabb_hit(rlo, rhi, lk.o, lk.inv, tmin, cull, tr);

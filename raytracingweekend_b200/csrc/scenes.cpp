@@ -117,8 +117,10 @@ bool random_balls_scene(rtw_builder* b, double aspect) {
     return s.finish({13, 2, 3}, {0, 0, 0}, 20.0, aspect, 0.0, 10.0, RTW_BG_GRADIENT);
 }
 
-// Scene/scene.h:176-249; `aluminum` enables the #if at :228-231 (BASELINE.json cfg4/5).
-bool cornell_box_scene(rtw_builder* b, double aspect, bool aluminum) {
+// Scene/scene.h:176-249; `aluminum` enables the #if at :228-231 (BASELINE.json cfg4/5); `glass` = false switches the #if at
+// :219-225 off: the short box (:212-217) stays and nothing but the area light is in `lights` ("cornell_two_boxes";
+// with `aluminum` it is the scene of the reference's Sampling/12.2.png, "cornell_aluminum_box").
+bool cornell_box_scene(rtw_builder* b, double aspect, bool aluminum, bool glass = true) {
     SceneCtx s{b};
     rtw_id red = lambert_const(b, 0.65f, 0.05f, 0.05f);
     rtw_id white = lambert_const(b, 0.73f, 0.73f, 0.73f);
@@ -132,9 +134,14 @@ bool cornell_box_scene(rtw_builder* b, double aspect, bool aluminum) {
     s.add(rtw_flip_normals(b, rtw_xz_rect(b, 0.0, 555.0, 0.0, 555.0, 555.0, white)));
     s.add(rtw_xz_rect(b, 0.0, 555.0, 0.0, 555.0, 0.0, white));
     s.add(rtw_flip_normals(b, rtw_xy_rect(b, 0.0, 555.0, 0.0, 555.0, 555.0, white)));
-    // the short box is pushed and popped again (scene.h:212-220); the glass sphere replaces it
-    s.add(rtw_sphere(b, 190, 90, 190, 90, rtw_dielectric(b, 1.5)));
-    s.lights.push_back(s.objects.back());
+    if (glass) {
+        // the short box is pushed and popped again (scene.h:212-220); the glass sphere replaces it
+        s.add(rtw_sphere(b, 190, 90, 190, 90, rtw_dielectric(b, 1.5)));
+        s.lights.push_back(s.objects.back());
+    } else {
+        double q0[3] = {0.0, 0.0, 0.0}, q1[3] = {165.0, 165.0, 165.0};
+        s.add(rtw_translate(b, rtw_rotate_y(b, rtw_box(b, q0, q1, white), -18.0), 130.0, 0.0, 65.0));  // scene.h:212-217
+    }
     rtw_id tall_mat = aluminum ? rtw_metal(b, 0.8, 0.85, 0.88, 0.0) : white;
     double p0[3] = {0.0, 0.0, 0.0}, p1[3] = {165.0, 330.0, 165.0};
     s.add(rtw_translate(b, rtw_rotate_y(b, rtw_box(b, p0, p1, tall_mat), 15.0), 265.0, 0.0, 295.0));
@@ -257,6 +264,8 @@ extern "C" int rtw_build_named_scene(rtw_builder* b, const char* name, double as
     else if (n == "random_balls_scene") ok = random_balls_scene(b, aspect);
     else if (n == "cornell_box_scene") ok = cornell_box_scene(b, aspect, false);
     else if (n == "cornell_box_aluminum") ok = cornell_box_scene(b, aspect, true);
+    else if (n == "cornell_two_boxes") ok = cornell_box_scene(b, aspect, false, false);
+    else if (n == "cornell_aluminum_box") ok = cornell_box_scene(b, aspect, true, false);
     else if (n == "two_perlin_spheres_earth") ok = two_perlin_spheres_earth(b, aspect, earth, enx, eny);
     else if (n == "book2_final_scene") ok = book2_final_scene(b, aspect, earth, enx, eny);
     else if (n == "cornell_smoke_scene") ok = cornell_smoke_scene(b, aspect);

@@ -346,6 +346,20 @@ cudaError_t launch_sorted_t(const DevScene& sc, const DevRenderParams& rp, float
 }
 }  // namespace
 
+#ifdef RTW_COUNT_EVENTS
+// diagnostics build: read and clear the traversal event counters of the render kernel (tools/count_tree_events.py)
+extern "C" int rtw_debug_events(unsigned long long* out, int n, int clear) {
+    unsigned long long h[8] = {};
+    if (cudaMemcpyFromSymbol(h, g_evc, sizeof h) != cudaSuccess) return -1;
+    for (int k = 0; k < n && k < 8; k++) out[k] = h[k];
+    if (clear) {
+        unsigned long long z[8] = {};
+        if (cudaMemcpyToSymbol(g_evc, z, sizeof z) != cudaSuccess) return -1;
+    }
+    return EVC_N;
+}
+#endif
+
 // spp * max_depth < 2^32: the per-pixel count of color() invocations is 32 bits
 bool sorted_supports(const DevRenderParams& rp) {
     return rp.spp_count <= (1 << 23) && rp.max_depth < (1 << 16) && (unsigned long long)rp.spp_count * (unsigned long long)rp.max_depth < (1ull << 32);

@@ -2,24 +2,71 @@
 
 One process per GPU (torchrun).  GPU g of G renders global sample indices [g*spp/G, (g+1)*spp/G) of EVERY pixel;
 Philox streams are keyed by the global sample index, so shards are disjoint by construction and the scene is
-simply replicated.  The only exchange step is `torch.distributed.reduce(accum, dst=0, SUM)` — ncclReduce of
-4*nx*ny floats over NVLink; rank 0 then tonemaps and writes the PPM.
+simply replicated.  The only exchange step is one ncclReduce of 4*nx*ny floats over NVLink; rank 0 then tonemaps and
+writes the PPM.  The data plane is the C ABI (`Communicator` = rtw_comm: ncclCommInitRank / ncclReduce inside
+librtw_b200.so; `Scene.render_sharded` = rtw_render_sharded); torch.distributed only carries the 128-byte NCCL id at
+start-up.  `reduce_accumulators` / `render_sharded` below are the torch.distributed twins used on CPU (gloo tests).
 """
 from __future__ import annotations
 
+import ctypes as C
 from typing import Optional, Tuple
 
 import torch
 import torch.distributed as dist
+
+from . import _lib
+
+
+class Communicator:
+    """rtw_comm: an NCCL communicator owned by librtw_b200.so (include/rtw_b200.h, section 4)."""
+
+    def __init__(self, comm_id: bytes, rank: int, world: int, device: int):
+        self._l = _lib.load()
+        buf = (C.c_uint8 * _lib.RTW_COMM_ID_BYTES).from_buffer_copy(comm_id)
+        self.handle = self._l.rtw_comm_create(buf, rank, world, device)
+        if not self.handle:
+            raise _lib.RtwError("rtw_comm_create: " + self._l.rtw_last_error().decode())
+        self.rank, self.world, self.device = rank, world, device
+
+    @staticmethod
+    def unique_id() -> bytes:
+        l = _lib.load()
+        buf = (C.c_uint8 * _lib.RTW_COMM_ID_BYTES)()
+        _lib.check(l.rtw_comm_unique_id(buf), "rtw_comm_unique_id")
+        return bytes(buf)
+
+    @classmethod
+    def from_torch(cls, rank: int, world: int, device: int, group=None) -> "Communicator":
+        """Rank 0 draws the NCCL id, torch.distributed broadcasts its 128 bytes, every rank joins."""
+        ids = [cls.unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ids, src=0, group=group)
+        return cls(ids[0], rank, world, device)
+
+    def reduce(self, accum_ptr: int, nx: int, ny: int, root: int = 0, stream: int = 0) -> None:
+        """In-place ncclReduce(SUM) of the [ny, nx, 4] float32 device buffer onto `root`, asynchronous on `stream`."""
+        _lib.check(self._l.rtw_reduce_accumulators(self.handle, C.c_void_p(accum_ptr), nx, ny, root, C.c_void_p(stream)),
+                   "rtw_reduce_accumulators")
+
+    def close(self):
+        if self.handle:
+            self._l.rtw_comm_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 def shard_range(spp: int, rank: int, world: int) -> Tuple[int, int]:
     """(spp_begin, spp_count) of `rank`: [rank*spp/world, (rank+1)*spp/world). Ranges tile [0, spp) exactly."""
     if world < 1 or not (0 <= rank < world) or spp < 0:
         raise ValueError("bad shard arguments")
-    lo = rank * spp // world
-    hi = (rank + 1) * spp // world
-    return lo, hi - lo
+    b, n = C.c_int(), C.c_int()
+    _lib.check(_lib.load().rtw_shard_range(spp, rank, world, C.byref(b), C.byref(n)), "rtw_shard_range")
+    return b.value, n.value
 
 
 def reduce_accumulators(accum: torch.Tensor, dst: int = 0, group=None) -> torch.Tensor:

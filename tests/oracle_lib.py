@@ -69,9 +69,9 @@ def _earth_arg(scene: str) -> str:
     return EARTH if scene in EARTH_SCENES else "-"
 
 
-def ref_run(args, threads=1, timeout=3600) -> str:
+def ref_run(args, threads=1, timeout=3600, binary=None) -> str:
     env = dict(os.environ, RTW_PPL_THREADS=str(threads))
-    return subprocess.run([REF_HARNESS] + [str(a) for a in args], check=True, capture_output=True, text=True, env=env, timeout=timeout).stdout
+    return subprocess.run([binary or REF_HARNESS] + [str(a) for a in args], check=True, capture_output=True, text=True, env=env, timeout=timeout).stdout
 
 
 def ref_flat(scene: str, aspect: float) -> bytes:
@@ -90,11 +90,11 @@ def ref_hits(scene: str, aspect: float, rays: np.ndarray, tmin="0.00100000004749
         return np.fromfile(po, dtype=np.float64).reshape(-1, 11)
 
 
-def ref_render(scene: str, nx, ny, spp, max_depth=100, threads=1, aspect=0.0):
-    """Reference image loop -> (sum[ny,nx,3], sumsq[ny,nx,3], info dict)."""
+def ref_render(scene: str, nx, ny, spp, max_depth=100, threads=1, aspect=0.0, binary=None):
+    """Reference image loop -> (sum[ny,nx,3], sumsq[ny,nx,3], info dict).  `binary`: another build of the same harness."""
     with tempfile.TemporaryDirectory() as d:
         po = os.path.join(d, "img.bin")
-        out = ref_run(["render", scene, aspect, _earth_arg(scene), nx, ny, spp, max_depth, po], threads=threads)
+        out = ref_run(["render", scene, aspect, _earth_arg(scene), nx, ny, spp, max_depth, po], threads=threads, binary=binary)
         a = np.fromfile(po, dtype=np.float64).reshape(ny, nx, 6)
         return a[..., :3].copy(), a[..., 3:].copy(), json.loads(out.strip().splitlines()[-1])
 

@@ -101,7 +101,8 @@ def test_intersect_batch_edge_cases(scenes):
                                              ("dielectric_scene", 48, 24, 8), ("random_balls_scene", 36, 24, 4),
                                              ("light_sample", 32, 32, 8), ("two_perlin_spheres_earth", 32, 32, 8),
                                              ("book2_final_scene", 32, 32, 4), ("cornell_smoke_scene", 40, 40, 8),
-                                             ("checker_spheres_scene", 48, 32, 8)])
+                                             ("checker_spheres_scene", 48, 32, 8), ("cornell_two_boxes", 40, 40, 8),
+                                             ("cornell_aluminum_box", 40, 40, 8)])
 def test_render_path_by_path_vs_oracle_philox(scenes, scene, nx, ny, spp):
     """Same Philox counters, same uniforms: the FP32 kernel must follow the FP64 oracle path for path.  A path may
     legitimately diverge when a branch decision (u < p, hit/miss at an edge) flips under FP32 rounding, so the test
@@ -269,6 +270,85 @@ def test_full_size_cfg4_properties(scenes):
     z = (np.abs(gm - rm) / np.sqrt(sigma2 + 1e-12))[ok]
     assert (z > 4).mean() < 0.005 and np.median(z) < 1.0, ((z > 4).mean(), np.median(z))
     assert np.allclose(gm[ok].mean(axis=0), rm[ok].mean(axis=0), rtol=0.02)
+
+
+def _full_size_properties(sc, b, nx, ny, spp, golden_file, G=8, seed=11, z4_limit=0.005, mean_rtol=0.02):
+    """Size-independent properties of one BASELINE.json config at its FULL stated shape (the cfg4 test above, generalised):
+    bit-reproducible launch; G spp shards trace exactly the rays of the unsharded render and sum to it; rays per path equals
+    the FP64 oracle's figure for this scene and aspect to 0.5 %; box-filtered down to the golden fixture's resolution it is
+    the image of the unmodified reference's serial CPU render (>= 4096 spp; per-pixel z-test, channel means)."""
+    full, st = sc.render(nx, ny, spp, seed=seed)
+    again, st2 = sc.render(nx, ny, spp, seed=seed)
+    assert np.array_equal(full, again, equal_nan=True) and st["rays"] == st2["rays"]
+    del again
+    assert st["paths"] == nx * ny * spp and np.all(full[..., 3] == spp)
+    g = np.load(os.path.join(GOLDEN, golden_file))
+    rnx, rny, rspp = int(g["nx"]), int(g["ny"]), int(g["spp"])
+    assert rspp >= 4096 and nx % rnx == 0 and ny % rny == 0 and nx // rnx == ny // rny
+    f = nx // rnx
+    acc = np.zeros((ny, nx, 4), np.float64)
+    rays, shard_means = 0, []
+    for k in range(G):
+        lo, hi = k * spp // G, (k + 1) * spp // G
+        part, stp = sc.render(nx, ny, hi - lo, spp_begin=lo, seed=seed)
+        acc += part
+        rays += stp["rays"]
+        p3 = np.nan_to_num(part[..., :3].astype(np.float64), nan=0.0, posinf=0.0, neginf=0.0) / (hi - lo)
+        shard_means.append(p3.reshape(rny, f, rnx, f, 3).mean(axis=(1, 3)))
+        del part
+    assert rays == st["rays"]
+    assert np.all(acc[..., 3] == spp)
+    fin = np.isfinite(full[..., :3]).all(axis=2)
+    assert fin.mean() > 0.9999 and np.array_equal(fin, np.isfinite(acc[..., :3]).all(axis=2))
+    assert np.allclose(acc[..., :3][fin], full[..., :3][fin], rtol=2e-5, atol=1e-3)
+    del acc
+    # rays per path against the FP64 oracle on the same scene and aspect (>= 600 k paths: standard error < 0.15 %)
+    onx = 96
+    ony = max(1, round(onx * ny / nx))
+    ospp = max(1, 600_000 // (onx * ony))
+    _, _, orays = ol.oracle_render(b, onx, ony, ospp, mode="philox", seed=seed)
+    rpp_o, rpp_g = orays / (onx * ony * ospp), st["rays"] / st["paths"]
+    print(f"rays/path gpu {rpp_g:.4f} oracle {rpp_o:.4f} ({(rpp_g / rpp_o - 1) * 100:+.3f} %)")
+    assert abs(rpp_g / rpp_o - 1.0) < 0.005, (rpp_g, rpp_o)
+    # image against the unmodified reference's render
+    img = np.where(fin[..., None], full[..., :3].astype(np.float64), 0.0) / spp
+    gm = img.reshape(rny, f, rnx, f, 3).mean(axis=(1, 3))
+    rm = g["sum"] / rspp
+    rvar = np.maximum(g["sumsq"] / rspp - rm * rm, 0.0) / rspp
+    ok = np.isfinite(rm).all(axis=2)
+    n_shard = f * f * (spp // G)
+    var_shard = np.var(np.stack(shard_means), axis=0, ddof=1)
+    sigma2 = np.maximum(rvar, var_shard * n_shard / rspp) + var_shard / G
+    z = (np.abs(gm - rm) / np.sqrt(sigma2 + 1e-12))[ok]
+    print(f"z-test: fraction(z>4) {(z > 4).mean():.5f}, median z {np.median(z):.3f}, channel means gpu {gm[ok].mean(axis=0)} ref {rm[ok].mean(axis=0)}")
+    assert (z > 4).mean() < z4_limit and np.median(z) < 1.0, ((z > 4).mean(), np.median(z))
+    assert np.allclose(gm[ok].mean(axis=0), rm[ok].mean(axis=0), rtol=mean_rtol)
+    return st
+
+
+def test_full_size_cfg1_properties(scenes):
+    """BASELINE.json configs[0]: Book-1 random scene (Scene/scene.h:98-174), 1200x800, 100 spp, depth 100."""
+    b, sc = scenes("random_balls_scene", 1200 / 800)
+    _full_size_properties(sc, b, 1200, 800, 100, "image_random_balls_scene.npz", G=4)
+
+
+def test_full_size_cfg2_properties(scenes):
+    """BASELINE.json configs[1]: two Perlin spheres + earth image_texture sphere, 800x800, 256 spp."""
+    b, sc = scenes("two_perlin_spheres_earth", 1.0)
+    _full_size_properties(sc, b, 800, 800, 256, "image_two_perlin_spheres_earth_40x40.npz")
+
+
+def test_full_size_cfg3_properties(scenes):
+    """BASELINE.json configs[2]: Book-2 final scene at its STATED shape: 800x800, 1024 spp, depth 100."""
+    b, sc = scenes("book2_final_scene", 1.0)
+    _full_size_properties(sc, b, 800, 800, 1024, "image_book2_final_scene_40x40.npz")
+
+
+def test_full_size_cfg5_properties(scenes):
+    """BASELINE.json configs[4]: Cornell box 3840x2160, 4096 spp (34 G paths), whole and as the 8 back-to-back spp shards of
+    the 8-GPU partition."""
+    b, sc = scenes("cornell_box_aluminum", 3840 / 2160)
+    _full_size_properties(sc, b, 3840, 2160, 4096, "image_cornell_box_aluminum_64x36.npz")
 
 
 def test_render_shapes_flags_and_depth(scenes):
