@@ -166,6 +166,8 @@ def load() -> C.CDLL:
             "(or __graft_entry__.build()). There is no CPU fallback for the render path.")
     lib = C.CDLL(LIB_PATH)
     for name, (res, args) in SIGNATURES.items():
+        if os.environ.get("RTW_B200_LIB") and not hasattr(lib, name):
+            continue  # an experimental / older build named explicitly (tools/ab_libs.sh): bind what it has
         fn = getattr(lib, name)  # AttributeError = ABI mismatch: fail loudly
         fn.restype = res
         fn.argtypes = args

@@ -321,6 +321,7 @@ int rtw_decode_jpeg(const uint8_t* data, size_t size, uint8_t* rgb8, size_t rgb8
             if (n >= 12 && memcmp(s, "Adobe", 5) == 0) adobe_transform = s[11];
         } else if (m == 0xDA) {  // SOS: the single scan of a baseline file
             if (!have_sof) return fail("SOS before SOF", RTW_ERR_INVALID);
+            if (n < 1) return fail("truncated SOS", RTW_ERR_INVALID);
             int ns = s[0];
             if (ns != (int)comps.size() || n < 1 + 2 * (size_t)ns + 3) return fail("non-interleaved multi-scan files are not supported");
             for (int c = 0; c < ns; c++) {
@@ -328,6 +329,8 @@ int rtw_decode_jpeg(const uint8_t* data, size_t size, uint8_t* rgb8, size_t rgb8
                 for (auto& cp : comps)
                     if (cp.id == cid) cp.td = s[2 + 2 * c] >> 4, cp.ta = s[2 + 2 * c] & 15;
             }
+            for (auto& cp : comps)  // four tables of each class exist (DHT above rejects th > 3): a selector beyond them is corrupt
+                if (cp.td > 3 || cp.ta > 3) return fail("bad Huffman table selector in SOS", RTW_ERR_INVALID);
             int hmax = 1, vmax = 1;
             for (auto& c : comps) hmax = c.h > hmax ? c.h : hmax, vmax = c.v > vmax ? c.v : vmax;
             const int mcux = (width + 8 * hmax - 1) / (8 * hmax), mcuy = (height + 8 * vmax - 1) / (8 * vmax);

@@ -45,7 +45,9 @@ template <uint32_t F, int SM>
 RTW_DEV void wf_start_path(const DevScene& sc, const DevRenderParams& rp, const WfParams& wp, uint32_t slot) {
     uint32_t pixel = kDeadPixel, sample = 0;
     int gi = 0, gj = 0;
-    for (int tries = 0; tries < 8; tries++) {
+    // until a work item lands inside the image or the items run out (the tiles are padded past the image: on a 1-pixel-wide
+    // frame 7 of 8 items are empty, and a slot must not be declared dead while items remain)
+    for (;;) {
         const unsigned mask = __activemask();
         const int lane = threadIdx.x & 31;
         const int leader = __ffs(mask) - 1;

@@ -63,6 +63,42 @@ def test_grayscale_restart_markers_and_errors():
         rtw.decode_jpeg(buf.getvalue()[:100])
 
 
+def test_corrupt_scan_headers_are_refused_and_fuzzed_files_never_crash():
+    """A malformed SOS (Huffman table selectors beyond the four tables, zero-length segment) or DHT must fail with an error,
+    never index outside the decoder's tables; random byte flips anywhere in the file either decode or fail cleanly."""
+    c = PIL.fromarray(_test_image(48, 32, 5))
+    buf = io.BytesIO()
+    c.save(buf, format="JPEG", quality=70, subsampling=0)
+    good = bytearray(buf.getvalue())
+    sos = good.index(b"\xff\xda")
+    ns = good[sos + 4]
+    assert ns == 3
+    for k in range(ns):  # each component's Td/Ta byte: selectors 4..15 do not exist
+        bad = bytearray(good)
+        bad[sos + 6 + 2 * k] = 0x7F
+        with pytest.raises(rtw._lib.RtwError):
+            rtw.decode_jpeg(bytes(bad))
+    bad = bytearray(good)
+    bad[sos + 2:sos + 4] = b"\x00\x02"  # SOS segment of length 2: no component count at all
+    with pytest.raises(rtw._lib.RtwError):
+        rtw.decode_jpeg(bytes(bad))
+    dht = good.index(b"\xff\xc4")
+    bad = bytearray(good)
+    bad[dht + 4] = 0x25  # table class 2 does not exist
+    with pytest.raises(rtw._lib.RtwError):
+        rtw.decode_jpeg(bytes(bad))
+    rng = np.random.default_rng(3)
+    for _ in range(300):
+        bad = bytearray(good)
+        for pos in rng.integers(2, len(good), size=rng.integers(1, 4)):
+            bad[pos] = rng.integers(0, 256)
+        try:
+            out = rtw.decode_jpeg(bytes(bad))
+            assert out.ndim == 3 and out.shape[2] == 3
+        except rtw._lib.RtwError:
+            pass
+
+
 def test_earth_jpg_decodes_to_the_pinned_texels():
     path = "/root/reference/RayTracingWeekend/earth.jpg"
     if not os.path.exists(path):
