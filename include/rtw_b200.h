@@ -303,6 +303,22 @@ int rtw_render(rtw_scene* s, const rtw_render_params* p, float* accum_host_rgba,
 int rtw_render_device(rtw_scene* s, const rtw_render_params* p, float* accum_dev_rgba, void* cuda_stream);
 int rtw_render_device_finish(rtw_scene* s, rtw_render_stats* stats);
 
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The wavefront render
+ * (rtw_render_device with RTW_FLAG_WAVEFRONT) with its scratch memory - the pool of path slots, the class queues and the
+ * counters - in a static device array of the library instead of allocated memory: the call allocates and frees NOTHING
+ * (no cudaMalloc / cudaFree / cudaMallocHost, no allocating library routine).  Limit: the array holds at most
+ * RTW_NOALLOC_MAX_POOL_SLOTS path slots (64 Ki slots, about 5.8 MB that every GPU which loads the library holds until the
+ * process exits); pool_slots = 0 picks the largest useful pool, a larger request fails with RTW_ERR_INVALID.  Any image size
+ * works (slots are refilled as paths end), a small pool only costs throughput.  The caller passes the scene (uploaded
+ * beforehand: set-up may allocate) and the device accumulator; results are those of rtw_render_device with
+ * RTW_FLAG_WAVEFRONT: identical ray counts, sums equal up to the order of the float adds.  Synchronous.
+ * ALL calls on one GPU share the array and it keeps the previous call's contents (the call clears what must start at
+ * zero): calls that overlap on the GPU - two host threads, two streams - race on it. */
+#define RTW_NOALLOC_MAX_POOL_SLOTS 65536u
+int rtw_render_device_noalloc(rtw_scene* s, const rtw_render_params* p, float* accum_dev_rgba, uint32_t pool_slots,
+                              void* cuda_stream, rtw_render_stats* stats);
+
 typedef struct rtw_ray { /* ray.h:17-20, FP32 */
     float ox, oy, oz, dx, dy, dz, time, pad_;
 } rtw_ray;

@@ -14,6 +14,7 @@ RTW_FLAG_WAVEFRONT = 1
 RTW_FLAG_AUTO = 8
 RTW_FLAG_ACCUMULATE = 2
 RTW_FLAG_DEBUG_RAY = 4
+RTW_NOALLOC_MAX_POOL_SLOTS = 65536
 RTW_COMM_ID_BYTES = 128
 
 
@@ -132,6 +133,7 @@ SIGNATURES = {
     "rtw_render": (C.c_int, [_P, C.POINTER(RenderParams), _P, C.POINTER(RenderStats)]),
     "rtw_render_device": (C.c_int, [_P, C.POINTER(RenderParams), _P, _P]),
     "rtw_render_device_finish": (C.c_int, [_P, C.POINTER(RenderStats)]),
+    "rtw_render_device_noalloc": (C.c_int, [_P, C.POINTER(RenderParams), _P, C.c_uint32, _P, C.POINTER(RenderStats)]),
     "rtw_intersect_batch": (C.c_int, [_P, _P, _P, C.c_int64, C.c_float, C.c_float]),
     "rtw_intersect_batch_device": (C.c_int, [_P, _P, _P, C.c_int64, C.c_float, C.c_float, _P]),
     "rtw_tonemap": (C.c_int, [_P, C.c_int, C.c_int, _P]),

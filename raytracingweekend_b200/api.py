@@ -204,6 +204,15 @@ class Scene:
                                          acc.ctypes.data_as(C.c_void_p) if acc is not None else None, C.byref(st)), "rtw_render_sharded")
         return acc, _stats(st)
 
+    def render_device_noalloc(self, accum_ptr: int, nx, ny, spp, spp_begin=0, max_depth=100, seed=0, flags=0, pool_slots: int = 0,
+                              stream: int = 0) -> dict:
+        """rtw_render_device_noalloc: the wavefront render on the library's static device scratch (allocates nothing;
+        pool_slots <= RTW_NOALLOC_MAX_POOL_SLOTS, 0 = largest useful).  Synchronous; returns the stats."""
+        p, st = self._params(nx, ny, spp, spp_begin, max_depth, seed, flags), RenderStats()
+        check(self._l.rtw_render_device_noalloc(self._s, C.byref(p), C.c_void_p(accum_ptr), pool_slots, C.c_void_p(stream), C.byref(st)),
+              "rtw_render_device_noalloc")
+        return _stats(st)
+
     def finish(self) -> dict:
         st = RenderStats()
         check(self._l.rtw_render_device_finish(self._s, C.byref(st)), "rtw_render_device_finish")

@@ -1040,6 +1040,59 @@ extern "C" int rtw_render(rtw_scene* s, const rtw_render_params* p, float* accum
     return RTW_OK;
 }
 
+// No-allocation variant of the wavefront render (no counterpart in the reference):
+// scratch = the library's static device array (wavefront.cu), nothing is allocated or freed by this call.
+extern "C" int rtw_render_device_noalloc(rtw_scene* s, const rtw_render_params* p, float* accum_dev, uint32_t pool_slots, void* cuda_stream,
+                                         rtw_render_stats* stats) {
+    int rc = check_params(s, p);
+    if (rc != RTW_OK) return rc;
+    if (!accum_dev) {
+        set_error("render_device_noalloc: null accumulator");
+        return RTW_ERR_INVALID;
+    }
+    if (s->pending) {
+        set_error("render_device_noalloc: the previous rtw_render_device of this scene has not been finished");
+        return RTW_ERR_INVALID;
+    }
+    const uint32_t max_slots = wavefront_noalloc_max_slots();
+    if (pool_slots > max_slots) {
+        set_error("render_device_noalloc: pool_slots = " + std::to_string(pool_slots) + " exceeds RTW_NOALLOC_MAX_POOL_SLOTS = " +
+                  std::to_string(max_slots) + " (the static device scratch holds no more; use rtw_render_device for bigger pools)");
+        return RTW_ERR_INVALID;
+    }
+    if (p->max_depth > 255 || (long long)p->spp_begin + p->spp_count >= (1 << 24)) {
+        set_error("render_device_noalloc: the wavefront pipeline packs (sample, bounce) into 24+8 bits: max_depth <= 255, samples < 2^24");
+        return RTW_ERR_INVALID;
+    }
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    cudaError_t e = cudaSetDevice(s->device);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
+    DevRenderParams rp{};
+    rp.nx = p->nx, rp.ny = p->ny, rp.spp_begin = p->spp_begin, rp.spp_count = p->spp_count, rp.max_depth = p->max_depth;
+    rp.flags = p->flags;
+    rp.seed_lo = (uint32_t)(p->seed & 0xffffffffu), rp.seed_hi = (uint32_t)(p->seed >> 32);
+    philox_round_keys(rp);
+    unsigned long long want = pool_slots ? pool_slots : max_slots;
+    const unsigned long long paths = (unsigned long long)p->nx * p->ny * p->spp_count;
+    if (want > paths) want = paths;        // never more slots than paths
+    want = (want + 255) & ~255ull;         // whole blocks, like rtw_render_device
+    if (want > max_slots) want = max_slots;
+    unsigned long long rays = 0;
+    int launches = 0;
+    if ((e = cudaEventRecord(s->ev0, st)) != cudaSuccess) return cuda_fail(e, "event");
+    if ((e = launch_wavefront_noalloc(s->dev, rp, (float4*)accum_dev, (uint32_t)want, &rays, &launches, st)) != cudaSuccess)
+        return cuda_fail(e, "wavefront (static scratch) launch");
+    if ((e = cudaEventRecord(s->ev1, st)) != cudaSuccess) return cuda_fail(e, "event");
+    if ((e = cudaEventSynchronize(s->ev1)) != cudaSuccess) return cuda_fail(e, "render kernels");
+    s->rendered = true;
+    if (stats) {
+        float ms = 0;
+        cudaEventElapsedTime(&ms, s->ev0, s->ev1);
+        stats->paths = paths, stats->rays = rays, stats->kernel_ms = ms, stats->kernel_launches = launches, stats->pad_ = 0;
+    }
+    return RTW_OK;
+}
+
 extern "C" int rtw_intersect_batch_device(rtw_scene* s, const rtw_ray* rays, rtw_hit* hits, int64_t n, float tmin, float tmax,
                                           void* cuda_stream) {
     if (!s || n < 0 || (n > 0 && (!rays || !hits))) {

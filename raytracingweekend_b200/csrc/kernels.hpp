@@ -28,6 +28,12 @@ size_t wavefront_scratch_bytes(uint32_t n_slots);
 cudaError_t launch_wavefront(const DevScene& sc, const DevRenderParams& rp, float4* accum, unsigned long long* ray_counter,
                              void* scratch, uint32_t n_slots, unsigned long long* host_flag, int* launches_out, cudaStream_t st);
 
+// The wavefront pipeline on the library's static device scratch (wavefront.cu): allocates nothing, synchronous,
+// n_slots <= wavefront_noalloc_max_slots(); `rays_out` is a HOST pointer.
+uint32_t wavefront_noalloc_max_slots();
+cudaError_t launch_wavefront_noalloc(const DevScene& sc, const DevRenderParams& rp, float4* accum, uint32_t n_slots,
+                                     unsigned long long* rays_out, int* launches_out, cudaStream_t st);
+
 // FFMA throughput of the current device in TFLOP/s (roofline denominator, measured not assumed).
 cudaError_t measure_fp32_peak(double* tflops);
 

@@ -27,6 +27,7 @@ namespace rtw {
 constexpr int kWfBlock = 256;
 constexpr int kWfClasses = 6;  // RTW_MAT_* (0..4) + miss/terminal (5)
 constexpr uint32_t kDeadPixel = 0xffffffffu;
+constexpr uint32_t kNoAllocMaxSlots = 65536;  // RTW_NOALLOC_MAX_POOL_SLOTS (include/rtw_b200.h): the static scratch holds this many path slots
 
 struct WfParams {
     float4 *A, *B, *C, *D;
@@ -278,6 +279,56 @@ cudaError_t launch_wavefront(const DevScene& sc, const DevRenderParams& rp, floa
     launches++;
     if (launches_out) *launches_out = launches;
     return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------ no-allocation variant
+// The same pipeline with its scratch (path-slot pool, class queues, counters, ray counter) in a file-scope device array
+// instead of memory from the pool allocator: for callers that may not allocate (CUDA graph capture around the call site,
+// tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// Every GPU that loads the library holds the array (kNoAllocBytes, ~5.8 MB) until the process exits.
+// ALL calls on a device share it and it keeps the last call's contents: what must start at zero (queue counters, work-item
+// and dead-slot counters, the ray counter) is cleared at the start of every call, the slot pool is fully rewritten by
+// wf_generate, queue entries are written before they are read.  Two calls that overlap on the GPU race on it.
+constexpr size_t kNoAllocRayCounterOff = ((size_t)kNoAllocMaxSlots * (4 * sizeof(float4) + kWfClasses * sizeof(uint32_t)) + 256 + 255) & ~(size_t)255;
+constexpr size_t kNoAllocBytes = kNoAllocRayCounterOff + 256;
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocBytes];
+
+// In host code `g_noalloc_scratch` is a host-side stand-in, not a device address: the address is resolved once per device,
+// with that device current, and only that pointer is handed to the kernels.
+static cudaError_t noalloc_scratch_ptr(uint8_t** out) {
+    static uint8_t* ptrs[64] = {};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    if (!ptrs[dev]) {
+        void* p = nullptr;
+        if ((e = cudaGetSymbolAddress(&p, g_noalloc_scratch)) != cudaSuccess) return e;
+        ptrs[dev] = (uint8_t*)p;
+    }
+    *out = ptrs[dev];
+    return cudaSuccess;
+}
+
+uint32_t wavefront_noalloc_max_slots() { return kNoAllocMaxSlots; }
+
+// Synchronous like launch_wavefront (the host polls the dead-slot counter).  Calls no cudaMalloc / cudaFree / cudaMallocHost:
+// the polls land in a stack variable.  n_slots <= kNoAllocMaxSlots (checked by the caller, re-checked here).
+cudaError_t launch_wavefront_noalloc(const DevScene& sc, const DevRenderParams& rp, float4* accum, uint32_t n_slots,
+                                     unsigned long long* rays_out, int* launches_out, cudaStream_t st) {
+    if (n_slots == 0 || n_slots > kNoAllocMaxSlots || wavefront_scratch_bytes(n_slots) > kNoAllocRayCounterOff) return cudaErrorInvalidValue;
+    uint8_t* base = nullptr;
+    cudaError_t e = noalloc_scratch_ptr(&base);
+    if (e != cudaSuccess) return e;
+    unsigned long long* ray_counter = (unsigned long long*)(base + kNoAllocRayCounterOff);
+    if ((e = cudaMemsetAsync(ray_counter, 0, sizeof(unsigned long long), st)) != cudaSuccess) return e;
+    unsigned long long host_flag[2] = {0, 0};  // pageable: the copies are staged by the driver, nothing is allocated here
+    if ((e = launch_wavefront(sc, rp, accum, ray_counter, base, n_slots, host_flag, launches_out, st)) != cudaSuccess) return e;
+    unsigned long long rays = 0;
+    if ((e = cudaMemcpyAsync(&rays, ray_counter, sizeof rays, cudaMemcpyDeviceToHost, st)) != cudaSuccess) return e;
+    if ((e = cudaStreamSynchronize(st)) != cudaSuccess) return e;
+    if (rays_out) *rays_out = rays;
+    return cudaSuccess;
 }
 
 }  // namespace rtw
