@@ -379,6 +379,15 @@ int rtw_write_png(const char* path, const double* canvas_rgb, int nx, int ny);
  * progressive / arithmetic / >2x subsampled files. */
 int rtw_decode_jpeg(const uint8_t* data, size_t size, uint8_t* rgb8, size_t rgb8_capacity, int* out_nx, int* out_ny);
 
+/* Known-answer hooks: the device functions of the render kernels, evaluated on caller-chosen inputs.
+ * rtw_philox4x32_10_batch: Philox4x32-10 (Salmon et al., SC'11; replaces the engines of utility.h:14-20) of n counters
+ *   (4 x uint32 each) under `key` -> n x 4 uint32; checked against the published Random123 vectors.
+ * rtw_sampler_batch: n samples of the bounded samplers that replace the reference's rejection loops, sample i drawn from
+ *   the Philox counter (pixel = i, sample = 0, bounce = 1, site): which = 0 uniform unit ball (utility.h:27-35), 1 unit
+ *   lens disk (camera.h:61-69), 2 cosine-weighted direction about +z (utility.h:54-67) -> n x 3 floats (host). */
+int rtw_philox4x32_10_batch(int device, const uint32_t* counters, int64_t n, uint64_t key, uint32_t* out);
+int rtw_sampler_batch(int device, int which, int64_t n, uint64_t seed, float* out_xyz);
+
 /* Measured FP32 FFMA throughput of `device` in TFLOP/s (roofline denominator). */
 int rtw_measure_fp32_peak(int device, double* tflops);
 /* Device utility: number of CUDA devices with compute capability 10.x (0 = none / no driver). */

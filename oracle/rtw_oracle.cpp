@@ -74,6 +74,8 @@ void philox4x32_10(const uint32_t c_in[4], const uint32_t k_in[2], uint32_t out[
 }
 
 enum { MODE_MINSTD = 0, MODE_PHILOX = 1 };
+double g_jitter_eps = 0.0;   // oracle_set_jitter: relative size of the per-ray perturbation (0 = off)
+uint64_t g_jitter_seed = 0;  // which perturbation
 enum { SITE_MAIN = 0, SITE_BALL = 1, SITE_LENS = 1, SITE_MEDIUM0 = 2 };
 
 struct Rng {
@@ -523,12 +525,21 @@ Onb onb_from_w(V n) {  // onb.h:32-38
 
 // random_in_unit_sphere (utility.h:27-35).  minstd: the rejection loop, constructor arguments drawn right to
 // left as g++ evaluates them; philox: direction * cbrt(U) from one draw (same distribution, no loop).
+// philox mode: uniform direction * cbrt(U) — the same distribution as the rejection loop (uniform in the unit ball)
+V ball_from_uniforms(double u0, double u1, double u2) {
+    double z = 1.0 - 2.0 * u0, r = std::sqrt(std::max(0.0, 1.0 - z * z)), phi = 2 * M_PI * u1, rad = cbrt(u2);
+    return mk(rad * r * cos(phi), rad * r * sin(phi), rad * z);
+}
+// philox mode of random_in_unit_disk (camera.h:61-69): polar (sqrt(U), 2 pi V) — uniform in the unit disk
+V disk_from_uniforms(double q0, double q1) {
+    double rad = sqrt(q0);
+    return mk(rad * cos(2 * M_PI * q1), rad * sin(2 * M_PI * q1), 0);
+}
 V random_in_unit_sphere(Rng& g, uint32_t bounce) {
     if (g.mode == MODE_PHILOX) {
         double u[4];
         g.philox(bounce, SITE_BALL, u);
-        double z = 1.0 - 2.0 * u[0], r = std::sqrt(std::max(0.0, 1.0 - z * z)), phi = 2 * M_PI * u[1], rad = cbrt(u[2]);
-        return mk(rad * r * cos(phi), rad * r * sin(phi), rad * z);
+        return ball_from_uniforms(u[0], u[1], u[2]);
     }
     V p;
     do {
@@ -675,8 +686,20 @@ struct Tracer {
     }
 
     // vec3 color(const ray&, const scene*, int depth)  (RayTracingWeekend.cpp:45-160); `bounce` = 1-based call index
-    V color(const Ray& r, int depth, uint32_t bounce) {
+    V color(const Ray& r_in, int depth, uint32_t bounce) {
         if (depth <= 0) return mk(0, 0, 0);
+        Ray r = r_in;
+        if (g_jitter_eps > 0 && rng.mode == MODE_PHILOX) {
+            // sensitivity probe (oracle_set_jitter): every ray entering color() is perturbed component-wise by a relative
+            // amount of FP32-rounding size, from Philox draws no sampler uses — a path whose result changes under this is one
+            // whose branch decisions FP32 arithmetic can legitimately flip
+            double a[4], b[4];
+            rng.philox(bounce, 0x7000u + 2u * (uint32_t)g_jitter_seed, a);
+            rng.philox(bounce, 0x7001u + 2u * (uint32_t)g_jitter_seed, b);
+            const double e = g_jitter_eps;
+            r.o = mk(r.o.x * (1 + e * (2 * a[0] - 1)), r.o.y * (1 + e * (2 * a[1] - 1)), r.o.z * (1 + e * (2 * a[2] - 1)));
+            r.d = mk(r.d.x * (1 + e * (2 * b[0] - 1)), r.d.y * (1 + e * (2 * b[1] - 1)), r.d.z * (1 + e * (2 * b[2] - 1)));
+        }
         rays++;
         ev(EV_RAY);
         Rec rec;
@@ -780,8 +803,7 @@ struct Tracer {
             rd = mk(0, 0, 0);
             if (c.lens_radius > 0) {
                 rng.philox(0, SITE_LENS, q);
-                double rad = c.lens_radius * sqrt(q[0]);
-                rd = mk(rad * cos(2 * M_PI * q[1]), rad * sin(2 * M_PI * q[1]), 0);
+                rd = c.lens_radius * disk_from_uniforms(q[0], q[1]);
             }
             time = c.time0 + u[2] * (c.time1 - c.time0);
         }
@@ -823,9 +845,9 @@ int oracle_event_count() { return EV_COUNT; }
 
 // world.hit() per ray, media skipped.  rays: n x 7 doubles (o, d, time).  out: n x 12 doubles
 // [hit, t, px, py, pz, nx, ny, nz, u, v, material, prim].
-void oracle_hit_batch(const rtw_flat_scene* fs, const double* rays, int64_t n, double tmin, double tmax, double* out) {
+static void hit_range(const rtw_flat_scene* fs, const double* rays, int64_t lo, int64_t hi, double tmin, double tmax, double* out) {
     World w{fs, nullptr, 0};
-    for (int64_t i = 0; i < n; i++) {
+    for (int64_t i = lo; i < hi; i++) {
         const double* q = rays + 7 * i;
         Ray r{mk(q[0], q[1], q[2]), mk(q[3], q[4], q[5]), q[6]};
         Rec rec;
@@ -838,6 +860,41 @@ void oracle_hit_batch(const rtw_flat_scene* fs, const double* rays, int64_t n, d
             o[5] = rec.normal.x, o[6] = rec.normal.y, o[7] = rec.normal.z, o[8] = rec.u, o[9] = rec.v;
             o[10] = rec.mat, o[11] = rec.prim;
         }
+    }
+}
+void oracle_hit_batch(const rtw_flat_scene* fs, const double* rays, int64_t n, double tmin, double tmax, double* out) {
+    // rays are independent and world_hit keeps no state between them: big batches are split over the host threads
+    const int threads = n >= (1 << 16) ? (int)std::max(1u, std::thread::hardware_concurrency()) : 1;
+    if (threads == 1) {
+        hit_range(fs, rays, 0, n, tmin, tmax, out);
+        return;
+    }
+    std::vector<std::thread> pool;
+    for (int t = 0; t < threads; t++) pool.emplace_back(hit_range, fs, rays, n * t / threads, n * (t + 1) / threads, tmin, tmax, out);
+    for (auto& t : pool) t.join();
+}
+
+// Sensitivity probe for the path-by-path parity tests: with eps > 0 a philox-mode render perturbs every ray by a relative
+// eps per component (tests use 2^-22, the size of accumulated FP32 rounding) — the pixels that change are the ones where
+// an FP32 kernel may legitimately leave the FP64 path.  eps = 0 switches it off.
+void oracle_set_jitter(double eps, uint64_t seed) { g_jitter_eps = eps, g_jitter_seed = seed; }
+
+// Known-answer hooks for the RNG and the philox-mode samplers (tests/test_rng_kat.py).
+void oracle_philox(const uint32_t* counter, const uint32_t* key, uint32_t* out) { philox4x32_10(counter, key, out); }
+// which: 0 unit ball (SITE_BALL draw), 1 lens disk (SITE_LENS draw), 2 cosine direction about +z (SITE_MAIN draw, r1 = u[2],
+// r2 = u[3] as in the lambertian branch).  Sample i uses the counter (pixel = i, sample = 0, bounce = 1, site).  out: n x 3.
+void oracle_sampler_batch(int which, int64_t n, uint64_t seed, double* out) {
+    Rng g;
+    g.mode = MODE_PHILOX;
+    g.seed_lo = (uint32_t)seed, g.seed_hi = (uint32_t)(seed >> 32);
+    for (int64_t i = 0; i < n; i++) {
+        g.pixel = (uint32_t)i, g.sample = 0;
+        double u[4];
+        V v;
+        if (which == 0) g.philox(1, SITE_BALL, u), v = ball_from_uniforms(u[0], u[1], u[2]);
+        else if (which == 1) g.philox(1, SITE_LENS, u), v = disk_from_uniforms(u[0], u[1]);
+        else g.philox(1, SITE_MAIN, u), v = random_cosine_direction(u[2], u[3]);
+        out[3 * i] = v.x, out[3 * i + 1] = v.y, out[3 * i + 2] = v.z;
     }
 }
 

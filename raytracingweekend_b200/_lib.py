@@ -150,6 +150,8 @@ SIGNATURES = {
     "rtw_shard_range": (C.c_int, [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "rtw_reduce_accumulators": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, _P]),
     "rtw_render_sharded": (C.c_int, [_P, _P, C.POINTER(RenderParams), C.c_int, _P, C.POINTER(RenderStats)]),
+    "rtw_philox4x32_10_batch": (C.c_int, [C.c_int, _P, C.c_int64, C.c_uint64, _P]),
+    "rtw_sampler_batch": (C.c_int, [C.c_int, C.c_int, C.c_int64, C.c_uint64, _P]),
     "rtw_device_count": (C.c_int, []),
     "rtw_measure_fp32_peak": (C.c_int, [C.c_int, C.POINTER(C.c_double)]),
 }

@@ -1140,6 +1140,49 @@ extern "C" int rtw_measure_fp32_peak(int device, double* tflops) {
     return RTW_OK;
 }
 
+// ------------------------------------------------------------------------------------------------ known-answer hooks
+extern "C" int rtw_philox4x32_10_batch(int device, const uint32_t* counters, int64_t n, uint64_t key, uint32_t* out) {
+    if (n < 0 || (n > 0 && (!counters || !out))) {
+        set_error("philox batch: bad arguments");
+        return RTW_ERR_INVALID;
+    }
+    if (n == 0) return RTW_OK;
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
+    DevRenderParams rp{};
+    rp.seed_lo = (uint32_t)key, rp.seed_hi = (uint32_t)(key >> 32);
+    philox_round_keys(rp);
+    uint4 *dc = nullptr, *dout = nullptr;
+    int rc = RTW_OK;
+    if ((e = dev_alloc((void**)&dc, n * 16)) != cudaSuccess || (e = dev_alloc((void**)&dout, n * 16)) != cudaSuccess ||
+        (e = cudaMemcpy(dc, counters, n * 16, cudaMemcpyHostToDevice)) != cudaSuccess || (e = launch_philox(dc, dout, n, rp)) != cudaSuccess ||
+        (e = cudaMemcpy(out, dout, n * 16, cudaMemcpyDeviceToHost)) != cudaSuccess)
+        rc = cuda_fail(e, "philox batch");
+    dev_free(dc);
+    dev_free(dout);
+    return rc;
+}
+
+extern "C" int rtw_sampler_batch(int device, int which, int64_t n, uint64_t seed, float* out_xyz) {
+    if (n < 0 || which < 0 || which > 2 || (n > 0 && !out_xyz)) {
+        set_error("sampler batch: bad arguments");
+        return RTW_ERR_INVALID;
+    }
+    if (n == 0) return RTW_OK;
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
+    DevRenderParams rp{};
+    rp.seed_lo = (uint32_t)seed, rp.seed_hi = (uint32_t)(seed >> 32);
+    philox_round_keys(rp);
+    float* d = nullptr;
+    int rc = RTW_OK;
+    if ((e = dev_alloc((void**)&d, n * 12)) != cudaSuccess || (e = launch_sampler(which, d, n, rp)) != cudaSuccess ||
+        (e = cudaMemcpy(out_xyz, d, n * 12, cudaMemcpyDeviceToHost)) != cudaSuccess)
+        rc = cuda_fail(e, "sampler batch");
+    dev_free(d);
+    return rc;
+}
+
 // ------------------------------------------------------------------------------------------------ multi-GPU
 // Samples-per-pixel sharding + ONE sum-reduce of the float4 accumulators onto the root.  The seam is still
 // RayTracingWeekend.cpp:211-250: the root ends up with the radiance sums of ALL samples and alone applies :241-244.

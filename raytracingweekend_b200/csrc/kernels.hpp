@@ -34,6 +34,10 @@ uint32_t wavefront_noalloc_max_slots();
 cudaError_t launch_wavefront_noalloc(const DevScene& sc, const DevRenderParams& rp, float4* accum, uint32_t n_slots,
                                      unsigned long long* rays_out, int* launches_out, cudaStream_t st);
 
+// Known-answer hooks (kernels.cu): Philox4x32-10 on given counters; the Philox-driven samplers (0 ball, 1 lens disk, 2 cosine).
+cudaError_t launch_philox(const uint4* counters, uint4* out, long long n, const DevRenderParams& rp);
+cudaError_t launch_sampler(int which, float* out, long long n, const DevRenderParams& rp);
+
 // FFMA throughput of the current device in TFLOP/s (roofline denominator, measured not assumed).
 cudaError_t measure_fp32_peak(double* tflops);
 

@@ -208,6 +208,14 @@ RTW_DEV V3 mixture_generate(const DevScene& sc, const SceneView& sv, V3 o, V3 n,
     return onb_local(uvw, mk(cs * st, sn * st, z));
 }
 
+// random_in_unit_disk (camera.h:61-69) without the rejection loop: polar (sqrt(u), 2*pi*v) is uniform in the unit disk.
+RTW_DEV void lens_disk(float u, float v, float& x, float& y) {
+    const float rad = sqrtf(u);
+    float sn, cs;
+    sincos_2pi(v, sn, cs);
+    x = rad * cs, y = rad * sn;
+}
+
 // ------------------------------------------------------------------------------------------------ camera
 // RayTracingWeekend.cpp:227-231 + camera::get_ray (camera.h:36-50).  The lens disk is sampled directly
 // (sqrt(u), 2*pi*v) instead of by rejection (camera.h:61-69) — same distribution — and skipped when aperture = 0.
@@ -220,10 +228,9 @@ RTW_DEV Ray camera_ray(const DevScene& sc, const DevRenderParams& rp, const Rng&
     V3 offset = mk(0.0f, 0.0f, 0.0f);
     if (c.lens_radius > 0.0f) {
         U4 q = rng.draw(0, SITE_LENS);
-        float rad = c.lens_radius * sqrtf(q.x);
-        float sn, cs;
-        sincos_2pi(q.y, sn, cs);
-        offset = (rad * cs) * mk(c.ux, c.uy, c.uz) + (rad * sn) * mk(c.wx, c.wy, c.wz);
+        float dx, dy;
+        lens_disk(q.x, q.y, dx, dy);
+        offset = (c.lens_radius * dx) * mk(c.ux, c.uy, c.uz) + (c.lens_radius * dy) * mk(c.wx, c.wy, c.wz);
     }
     Ray ray;
     ray.time = fmaf(r.z, c.time1 - c.time0, c.time0);
