@@ -49,24 +49,7 @@ IMAGES_SHAPED = {"two_perlin_spheres_earth": (40, 40, 4096),   # cfg2 800x800, f
                  "cornell_box_aluminum": (64, 36, 4096)}       # cfg5 3840x2160, factor 60
 
 
-def fixed_rays(builder, n: int, seed: int) -> np.ndarray:
-    """Half pinhole-grid primary rays (pixel centres), half random origins/directions around the view volume."""
-    rng = np.random.default_rng(seed)
-    cam = builder.flatten().contents.camera
-    o, llc = np.array(cam.origin), np.array(cam.lower_left_corner)
-    h, v = np.array(cam.horizontal), np.array(cam.vertical)
-    m = int(np.sqrt(n // 2))
-    s, t = np.meshgrid((np.arange(m) + 0.5) / m, (np.arange(m) + 0.5) / m)
-    d = llc + s.reshape(-1, 1) * h + t.reshape(-1, 1) * v - o
-    d /= np.linalg.norm(d, axis=1, keepdims=True)
-    prim = np.concatenate([np.tile(o, (m * m, 1)), d, rng.random((m * m, 1))], axis=1)
-    ctr = o + d.mean(0) * np.linalg.norm(llc + 0.5 * h + 0.5 * v - o) * 60
-    k = n - m * m
-    ro = ctr + (rng.random((k, 3)) - 0.5) * np.linalg.norm(ctr - o) * 1.5
-    rd = rng.normal(size=(k, 3))
-    rays = np.concatenate([prim, np.concatenate([ro, rd, rng.random((k, 1))], axis=1)])
-    # keep every value exactly representable in FP32 so GPU and CPU see the same rays
-    return rays.astype(np.float32).astype(np.float64)
+fixed_rays = ol.fixed_rays  # the SURVEY 8d batch construction, shared with tests/test_gpu_parity.py
 
 
 def builder_for(name: str, aspect: float):

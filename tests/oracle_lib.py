@@ -118,3 +118,44 @@ def oracle_funcs(tables: np.ndarray) -> np.ndarray:
     t = np.ascontiguousarray(tables, dtype=np.float64)
     n = oracle().oracle_funcs(t.ctypes.data, out.ctypes.data, out.size)
     return out[:n]
+
+
+def set_jitter(eps: float, seed: int = 0) -> None:
+    """oracle_set_jitter: per-ray relative perturbation of philox-mode renders (sensitivity probe); 0 switches it off."""
+    o = oracle()
+    o.oracle_set_jitter.argtypes = [C.c_double, C.c_uint64]
+    o.oracle_set_jitter.restype = None
+    o.oracle_set_jitter(float(eps), int(seed))
+
+
+def fixed_rays(builder, n: int, seed: int) -> np.ndarray:
+    """SURVEY 8d ray batch: half pinhole-grid primary rays (pixel centres of an m x m grid, m*m = n/2), half rays with random
+    origins around the view volume and uniform directions; times uniform in [0, 1).  Every value is exactly representable in
+    FP32, so GPU and CPU see the same rays.  (tests/golden/make_golden.py draws the reference-held 4000-ray batches the same way.)"""
+    rng = np.random.default_rng(seed)
+    cam = builder.flatten().contents.camera
+    o, llc = np.array(cam.origin), np.array(cam.lower_left_corner)
+    h, v = np.array(cam.horizontal), np.array(cam.vertical)
+    m = int(np.sqrt(n // 2))
+    s, t = np.meshgrid((np.arange(m) + 0.5) / m, (np.arange(m) + 0.5) / m)
+    d = llc + s.reshape(-1, 1) * h + t.reshape(-1, 1) * v - o
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    prim = np.concatenate([np.tile(o, (m * m, 1)), d, rng.random((m * m, 1))], axis=1)
+    ctr = o + d.mean(0) * np.linalg.norm(llc + 0.5 * h + 0.5 * v - o) * 60
+    k = n - m * m
+    ro = ctr + (rng.random((k, 3)) - 0.5) * np.linalg.norm(ctr - o) * 1.5
+    rd = rng.normal(size=(k, 3))
+    rays = np.concatenate([prim, np.concatenate([ro, rd, rng.random((k, 1))], axis=1)])
+    return rays.astype(np.float32).astype(np.float64)
+
+
+def record_stats(name: str, stats: dict) -> None:
+    """Observed parity numbers of a GPU test run (flip counts, error maxima, divergent-pixel fractions): appended to
+    gpurun_out/parity_stats.jsonl so that the thresholds in the tests can be set from — and checked against — measurements."""
+    try:
+        d = os.path.join(ROOT, "gpurun_out")
+        os.makedirs(d, exist_ok=True)
+        with open(os.path.join(d, "parity_stats.jsonl"), "a") as f:
+            f.write(json.dumps(dict(stats, test=name)) + "\n")
+    except OSError:
+        pass
