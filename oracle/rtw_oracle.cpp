@@ -881,7 +881,7 @@ void oracle_set_jitter(double eps, uint64_t seed) { g_jitter_eps = eps, g_jitter
 
 // Known-answer hooks for the RNG and the philox-mode samplers (tests/test_rng_kat.py).
 void oracle_philox(const uint32_t* counter, const uint32_t* key, uint32_t* out) { philox4x32_10(counter, key, out); }
-// which: 0 unit ball (SITE_BALL draw), 1 lens disk (SITE_LENS draw), 2 cosine direction about +z (SITE_MAIN draw, r1 = u[2],
+// which: 0 unit ball (SITE_BALL draw), 1 lens disk (SITE_LENS draw), 2 cosine_pdf::generate about +z (SITE_MAIN draw, r1 = u[2],
 // r2 = u[3] as in the lambertian branch).  Sample i uses the counter (pixel = i, sample = 0, bounce = 1, site).  out: n x 3.
 void oracle_sampler_batch(int which, int64_t n, uint64_t seed, double* out) {
     Rng g;
@@ -893,7 +893,7 @@ void oracle_sampler_batch(int which, int64_t n, uint64_t seed, double* out) {
         V v;
         if (which == 0) g.philox(1, SITE_BALL, u), v = ball_from_uniforms(u[0], u[1], u[2]);
         else if (which == 1) g.philox(1, SITE_LENS, u), v = disk_from_uniforms(u[0], u[1]);
-        else g.philox(1, SITE_MAIN, u), v = random_cosine_direction(u[2], u[3]);
+        else g.philox(1, SITE_MAIN, u), v = onb_from_w(mk(0, 0, 1)).local(random_cosine_direction(u[2], u[3]));  // cosine_pdf about +z (pdf.h:18, :26-29)
         out[3 * i] = v.x, out[3 * i + 1] = v.y, out[3 * i + 2] = v.z;
     }
 }
