@@ -293,58 +293,175 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
         return same(P[1], x0, x1, y0, y1, z0) && same(P[2], x0, x1, z0, z1, y1) && same(P[3], x0, x1, z0, z1, y0) &&
                same(P[4], y0, y1, z0, z1, x1) && same(P[5], y0, y1, z0, z1, x0);
     };
+    // Room records: a set of >= 3 axis-aligned rects of one run that are faces of ONE box (the five walls of the Cornell
+    // room, Scene/scene.h:197-210: at most one rect per face, extents exactly the box's) is tested by the render kernels with
+    // one slab test instead of one plane test per wall: the nearest rect hit is the entry face when the ray starts outside and
+    // that face exists, else the exit face (the box is convex, so no other face can be nearer); t is the very expression of
+    // the rect test.  Same record as a box plus a table of the six face ids (-1 = no such wall).  Only formed when the run's
+    // other rects all come before (or all after) the room's in list order, so that the "later rect wins an exact tie" rule
+    //  is kept by the order of the two groups; intersect_batch keeps the rect-by-rect order either way.
+    // Measured on B200 (profiles/r2_ab_rooms.txt): NEUTRAL — Cornell + glass + aluminium 6.60 Gpaths/s without, 6.56 with: the
+    // slab test saves ~60 of the five plane tests' ~110 instructions per ray, and splitting the run into "room" and "the rest"
+    // adds a group (~30 instructions of header loads and kind-loop bounds) — so it is opt-in (RTW_ROOM_PRIMS=1), off by default.
+    static const bool use_rooms = [] { const char* v = getenv("RTW_ROOM_PRIMS"); return v && atoi(v) != 0; }();
+    struct Room {
+        double lo[3], hi[3];
+        int face[6];  // box face order (builder.cpp K_BOX): z = hi, z = lo, y = hi, y = lo, x = hi, x = lo
+        int n = 0;
+    };
+    auto rect_axes = [&](int p, int ax[3]) {  // in-plane axes a, b and the normal axis
+        const int t = fs->prims[p].type;
+        if (t == RTW_PRIM_XY_RECT) ax[0] = 0, ax[1] = 1, ax[2] = 2;
+        else if (t == RTW_PRIM_XZ_RECT) ax[0] = 0, ax[1] = 2, ax[2] = 1;
+        else ax[0] = 1, ax[1] = 2, ax[2] = 0;
+    };
+    auto find_room = [&](const std::vector<int>& members, Room& best) {
+        best.n = 0;
+        std::vector<int> rects;
+        for (int p : members)
+            if (fs->prims[p].type >= RTW_PRIM_XY_RECT && fs->prims[p].type <= RTW_PRIM_YZ_RECT) rects.push_back(p);
+        if (!use_rooms || rects.size() < 3 || rects.size() > 64) return;
+        for (int seed : rects) {
+            // the seed fixes two ranges; the third comes from another rect's in-plane range that ends on the seed's plane
+            Room r;
+            bool known[3] = {false, false, false};
+            for (int k = 0; k < 6; k++) r.face[k] = -1;
+            int ax[3];
+            rect_axes(seed, ax);
+            const double* v = fs->prims[seed].v;
+            if (!(v[0] < v[1] && v[2] < v[3])) continue;
+            r.lo[ax[0]] = v[0], r.hi[ax[0]] = v[1], r.lo[ax[1]] = v[2], r.hi[ax[1]] = v[3];
+            known[ax[0]] = known[ax[1]] = true;
+            for (int q : rects) {
+                int bx[3];
+                rect_axes(q, bx);
+                const double* w = fs->prims[q].v;
+                for (int e = 0; e < 2 && !known[ax[2]]; e++)
+                    if (bx[e] == ax[2] && w[2 * e] < w[2 * e + 1] && (v[4] == w[2 * e] || v[4] == w[2 * e + 1]))
+                        r.lo[ax[2]] = w[2 * e], r.hi[ax[2]] = w[2 * e + 1], known[ax[2]] = true;
+            }
+            if (!known[ax[2]]) continue;
+            for (int q : rects) {
+                int bx[3];
+                rect_axes(q, bx);
+                const double* w = fs->prims[q].v;
+                if (w[0] != r.lo[bx[0]] || w[1] != r.hi[bx[0]] || w[2] != r.lo[bx[1]] || w[3] != r.hi[bx[1]]) continue;
+                const bool at_hi = w[4] == r.hi[bx[2]], at_lo = w[4] == r.lo[bx[2]];
+                if (!at_hi && !at_lo) continue;
+                const int f = (bx[2] == 2 ? 0 : (bx[2] == 1 ? 2 : 4)) + (at_hi ? 0 : 1);
+                if (r.face[f] >= 0) {  // two rects on one face: not a room
+                    r.n = -1000;
+                    break;
+                }
+                r.face[f] = q, r.n++;
+            }
+            if (r.n > best.n) best = r;
+        }
+        if (best.n < 3) {
+            best.n = 0;
+            return;
+        }
+        // a rect of the run that is not a face but lies in a face's plane could tie with it exactly: leave such runs alone
+        int lo_idx = 1 << 30, hi_idx = -1;
+        for (int k = 0; k < 6; k++)
+            if (best.face[k] >= 0) lo_idx = std::min(lo_idx, best.face[k]), hi_idx = std::max(hi_idx, best.face[k]);
+        bool before = true, after = true;
+        for (int q : rects) {
+            bool is_face = false;
+            for (int k = 0; k < 6; k++) is_face |= best.face[k] == q;
+            if (is_face) continue;
+            int bx[3];
+            rect_axes(q, bx);
+            const double k4 = fs->prims[q].v[4];
+            if (k4 == best.lo[bx[2]] || k4 == best.hi[bx[2]]) {
+                best.n = 0;
+                return;
+            }
+            before &= q < lo_idx, after &= q > hi_idx;
+        }
+        if (!before && !after) best.n = 0;
+        else if (!before) best.n = -best.n;  // n < 0: the run's other members go AFTER the room
+    };
+    // one group of records for `members` (ascending list order, one transform chain); `box_first` >= 0: also the box record of
+    // the six rects starting there; `room`: also a room record
+    auto emit_group = [&](const std::vector<int>& members, int box_first, const Room* room) {
+        DevGroup g{};
+        g.xf = fs->prims[members[0]].xf;
+        g.sph0 = (int)recs.size();
+        const int kinds[5] = {RTW_PRIM_SPHERE, RTW_PRIM_MOVING_SPHERE, RTW_PRIM_XY_RECT, RTW_PRIM_XZ_RECT, RTW_PRIM_YZ_RECT};
+        int32_t* ends[5] = {&g.sph1, &g.msph1, &g.xy1, &g.xz1, &g.yz1};
+        for (int k = 0; k < 5; k++) {
+            for (int p : members) {
+                if (fs->prims[p].type != kinds[k]) continue;
+                DevRec r{};
+                r.a = pa[p];
+                if (k == 0) {
+                    int id = p;
+                    if (pm[p] & PM_PRECISE) {
+                        id |= REC_PRECISE;
+                        r.b.x = pb[p].w;  // pd index bits (-> byte offset below)
+                    }
+                    r.b.w = __int_as_float_host(id);
+                } else if (k == 1) {
+                    r.b = make_float4(pb[p].x, pb[p].y, pb[p].z, __int_as_float_host(p));
+                } else {
+                    r.b = make_float4(pb[p].x, 0.0f, 0.0f, __int_as_float_host(p));
+                }
+                recs.push_back(r);
+            }
+            *ends[k] = (int)recs.size();
+        }
+        if (box_first >= 0) {
+            const rtw_flat_prim& xy1r = fs->prims[box_first];      // x0 x1 y0 y1 | z1
+            const rtw_flat_prim& xy0r = fs->prims[box_first + 1];  // z0
+            DevRec r{};
+            // the same FP32 constants as the rect records (round to nearest), so t is bit-identical to the rect test
+            r.a = make_float4((float)xy1r.v[0], (float)xy1r.v[2], (float)xy0r.v[4], 0.0f);
+            r.b = make_float4((float)xy1r.v[1], (float)xy1r.v[3], (float)xy1r.v[4], __int_as_float_host(box_first));
+            recs.push_back(r);
+        }
+        if (room) {
+            DevRec r{}, ids{};
+            r.a = make_float4((float)room->lo[0], (float)room->lo[1], (float)room->lo[2], __int_as_float_host(1));  // a.w != 0: room
+            r.b = make_float4((float)room->hi[0], (float)room->hi[1], (float)room->hi[2], 0.0f);
+            ids.a = make_float4(__int_as_float_host(room->face[0]), __int_as_float_host(room->face[1]), __int_as_float_host(room->face[2]),
+                                __int_as_float_host(room->face[3]));
+            ids.b = make_float4(__int_as_float_host(room->face[4]), __int_as_float_host(room->face[5]), 0.0f, 0.0f);
+            recs.push_back(r);
+            recs.push_back(ids);  // the face-id table rides in the next record slot (the box loop skips it)
+        }
+        g.box1 = (int)recs.size();
+        groups.push_back(g);
+    };
     auto add_groups_of = [&](const std::vector<int>& ids, int& first_group, int& end_group) {
         first_group = (int)groups.size();
         size_t i = 0;
         while (i < ids.size()) {
             // a run = consecutive primitives with one transform chain, cut so that a box is a run of its own
             size_t j = i;
-            bool box = is_box_at(ids, i, ids.size());
+            const bool box = is_box_at(ids, i, ids.size());
             if (box) {
                 j = i + 6;
             } else {
                 while (j < ids.size() && fs->prims[ids[j]].xf == fs->prims[ids[i]].xf && !is_box_at(ids, j, ids.size())) j++;
             }
-            DevGroup g{};
-            g.xf = fs->prims[ids[i]].xf;
-            g.sph0 = (int)recs.size();
-            const int kinds[5] = {RTW_PRIM_SPHERE, RTW_PRIM_MOVING_SPHERE, RTW_PRIM_XY_RECT, RTW_PRIM_XZ_RECT, RTW_PRIM_YZ_RECT};
-            int32_t* ends[5] = {&g.sph1, &g.msph1, &g.xy1, &g.xz1, &g.yz1};
-            for (int k = 0; k < 5; k++) {
-                for (size_t q = i; q < j; q++) {
-                    const int p = ids[q];
-                    if (fs->prims[p].type != kinds[k]) continue;
-                    DevRec r{};
-                    r.a = pa[p];
-                    if (k == 0) {
-                        int id = p;
-                        if (pm[p] & PM_PRECISE) {
-                            id |= REC_PRECISE;
-                            r.b.x = pb[p].w;  // pd index bits (-> byte offset below)
-                        }
-                        r.b.w = __int_as_float_host(id);
-                    } else if (k == 1) {
-                        r.b = make_float4(pb[p].x, pb[p].y, pb[p].z, __int_as_float_host(p));
-                    } else {
-                        r.b = make_float4(pb[p].x, 0.0f, 0.0f, __int_as_float_host(p));
-                    }
-                    recs.push_back(r);
+            std::vector<int> members(ids.begin() + i, ids.begin() + j);
+            Room room;
+            room.n = 0;
+            if (!box) find_room(members, room);
+            if (room.n != 0) {
+                std::vector<int> faces, others;
+                for (int p : members) {
+                    bool is_face = false;
+                    for (int k = 0; k < 6; k++) is_face |= room.face[k] == p;
+                    (is_face ? faces : others).push_back(p);
                 }
-                *ends[k] = (int)recs.size();
+                if (room.n > 0 && !others.empty()) emit_group(others, -1, nullptr);
+                emit_group(faces, -1, &room);
+                if (room.n < 0 && !others.empty()) emit_group(others, -1, nullptr);
+            } else {
+                emit_group(members, box ? ids[i] : -1, nullptr);
             }
-            if (box) {
-                const rtw_flat_prim& xy1r = fs->prims[ids[i]];      // x0 x1 y0 y1 | z1
-                const rtw_flat_prim& xy0r = fs->prims[ids[i + 1]];  // z0
-                const rtw_flat_prim& xz1r = fs->prims[ids[i + 2]];  // x0 x1 z0 z1 | y1
-                DevRec r{};
-                // the same FP32 constants as the rect records (round to nearest), so t is bit-identical to the rect test
-                r.a = make_float4((float)xy1r.v[0], (float)xy1r.v[2], (float)xy0r.v[4], 0.0f);
-                r.b = make_float4((float)xy1r.v[1], (float)xy1r.v[3], (float)xy1r.v[4], __int_as_float_host(ids[i]));
-                (void)xz1r;
-                recs.push_back(r);
-            }
-            g.box1 = (int)recs.size();
-            groups.push_back(g);
             i = j;
         }
         end_group = (int)groups.size();
@@ -857,7 +974,7 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
     rtw_scene* s = new (std::nothrow) rtw_scene();
     if (!s) return nullptr;
     s->device = device;
-    cudaError_t err[] = {s->blob.upload(blob), s->texels.upload(texels), dev_alloc((void**)&s->d_counter, sizeof(unsigned long long)),
+    cudaError_t err[] = {s->blob.upload(blob), s->texels.upload(texels), dev_alloc((void**)&s->d_counter, 2 * sizeof(unsigned long long)),  // [0] rays, [1] render_sorted's tile counter
                          cudaEventCreate(&s->ev0), cudaEventCreate(&s->ev1)};
     for (cudaError_t x : err)
         if (x != cudaSuccess) {
@@ -942,7 +1059,7 @@ extern "C" int rtw_render_device(rtw_scene* s, const rtw_render_params* p, float
     rp.flags = p->flags;
     rp.seed_lo = (uint32_t)(p->seed & 0xffffffffu), rp.seed_hi = (uint32_t)(p->seed >> 32);
     philox_round_keys(rp);
-    if ((e = cudaMemsetAsync(s->d_counter, 0, sizeof(unsigned long long), st)) != cudaSuccess) return cuda_fail(e, "memset");
+    if ((e = cudaMemsetAsync(s->d_counter, 0, 2 * sizeof(unsigned long long), st)) != cudaSuccess) return cuda_fail(e, "memset");
     if ((e = cudaEventRecord(s->ev0, st)) != cudaSuccess) return cuda_fail(e, "event");
     int launches = 1;
     bool wavefront = (p->flags & RTW_FLAG_WAVEFRONT) != 0;

@@ -406,6 +406,42 @@ RTW_DEV void box_update(float4 lo, float4 hi, const RayK& k, float tmin, float& 
     }
 }
 
+// One slab test for the walls of a "room": >= 3 rects that are faces of one box, at most one per face (api.cu find_room; the
+// Cornell room is five of six).  Record = box record with a.w != 0, followed by the table of the six face ids in box face
+// order {z = hi, z = lo, y = hi, y = lo, x = hi, x = lo}, -1 = no such wall.  The nearest wall hit with t in [tmin, t_best]
+// is the ENTRY face if the ray starts before it and that wall exists, else the EXIT face (the box is convex: no other face
+// can lie between); t is the expression of rect_update, so it is bit-identical.  At an edge (two planes at the same t) the
+// wall that is later in the list wins, like the rect loop's `t <= t_best` in list order.
+template <int SM>
+RTW_DEV void room_update(const SceneView& sv, uint32_t ids_addr, float4 lo, float4 hi, const RayK& k, float tmin, float& t_best,
+                         int& prim_best) {
+    RTW_EV(EVC_BOX, 1);
+    const float tx0 = (lo.x - k.o.x) * k.inv.x, tx1 = (hi.x - k.o.x) * k.inv.x;
+    const float ty0 = (lo.y - k.o.y) * k.inv.y, ty1 = (hi.y - k.o.y) * k.inv.y;
+    const float tz0 = (lo.z - k.o.z) * k.inv.z, tz1 = (hi.z - k.o.z) * k.inv.z;
+    const float nx = fminf(tx0, tx1), fx = fmaxf(tx0, tx1);
+    const float ny = fminf(ty0, ty1), fy = fmaxf(ty0, ty1);
+    const float nz = fminf(tz0, tz1), fz = fmaxf(tz0, tz1);
+    const float te = fmaxf(fmaxf(nx, ny), nz), tf = fminf(fminf(fx, fy), fz);
+    if (!(te <= tf) || !(tf >= tmin) || !(te <= t_best)) return;  // past the box, behind the ray, or beyond the closest hit
+    const float4 ia = hot4_abs<SM>(sv, ids_addr), ib = hot4_abs<SM>(sv, ids_addr + 16);
+    const bool xl = tx0 <= tx1, yl = ty0 <= ty1, zl = tz0 <= tz1;  // the lo plane is the near one on this axis
+    const int x_near = fi(xl ? ib.y : ib.x), x_far = fi(xl ? ib.x : ib.y);
+    const int y_near = fi(yl ? ia.w : ia.z), y_far = fi(yl ? ia.z : ia.w);
+    const int z_near = fi(zl ? ia.y : ia.x), z_far = fi(zl ? ia.x : ia.y);
+    int id = -1;
+    float t = te;
+    if (te >= tmin) id = max(max(nx == te ? x_near : -1, ny == te ? y_near : -1), nz == te ? z_near : -1);
+    if (id < 0) {  // started inside, or entered through an open face
+        t = tf;
+        id = max(max(fx == tf ? x_far : -1, fy == tf ? y_far : -1), fz == tf ? z_far : -1);
+    }
+    if (id >= 0 && t <= t_best) {
+        t_best = t;
+        prim_best = id;
+    }
+}
+
 // The five kind loops of one group, for ray constants `k` already in the group's frame.  BOXREC (render kernels): a group
 // that carries a box record is tested with it instead of its six rects.
 template <uint32_t F, int SM, bool BOXREC>
@@ -419,7 +455,15 @@ RTW_DEV void test_group_kinds(const SceneView& sv, float4 g0, float4 g1, const R
         const uint32_t box1 = hot_abs<SM>(sv, (uint32_t)fi(g1.w));
         if (box1 != yz1) {  // warp-uniform
 #pragma unroll 1
-            for (uint32_t r = yz1; r < box1; r += 32) box_update(hot4_abs<SM>(sv, r), hot4_abs<SM>(sv, r + 16), k, tmin, t_best, prim_best);
+            for (uint32_t r = yz1; r < box1; r += 32) {
+                const float4 lo = hot4_abs<SM>(sv, r), hi = hot4_abs<SM>(sv, r + 16);
+                if (fi(lo.w) != 0) {  // warp-uniform: a room record, its face-id table in the next slot
+                    room_update<SM>(sv, r + 32, lo, hi, k, tmin, t_best, prim_best);
+                    r += 32;
+                } else {
+                    box_update(lo, hi, k, tmin, t_best, prim_best);
+                }
+            }
             return;
         }
     }

@@ -15,14 +15,13 @@
 //            lanes) -> classify -> store state -> push.  Terminal units add their radiance and start 32 new camera
 //            rays on the spot, so camera maths also runs at full lanes.
 //
-// Ring capacity = number of slots is enough only because a consumer reads (and clears) its entries right after the CAS
-// that claimed them: entries that are claimed but not yet read still occupy ring positions behind the head, and while they
-// do the tail may run at most `capacity - 32` ahead of the head.  A warp that kept claimed entries unread across a whole
-// unit (e.g. claiming 64 and running two units) lets other warps cycle the head forward until producers wrap onto them —
-// lost slots, `live` never reaches 0, the block never ends (measured: that variant hung).  Do not batch claims without
-// doubling the rings.
+// Rings: capacity >= number of slots.  A consumer reads (and clears) its entries right after the CAS that claimed them, and
+// a producer WAITS until its target position is empty before it writes (one LDS per push), so a delayed consumer can never
+// be overwritten: the worst a slow warp causes is a short producer spin, not a lost slot (round 1 relied on warp timing
+// here, and a variant that batched two claims hung).  Two producers that target the same position one lap apart may land
+// in either order — entries are only slot ids of one class, any order is correct.
 //
-// Per-pixel sums are 64-bit fixed point (2^-24) in shared memory: integer adds commute, so the image stays
+// Per-pixel sums are 64-bit fixed point (2^-24) in shared memory (kept as two 32-bit words, see the adds): integer adds commute, so the image stays
 // bit-reproducible although units run in a timing-dependent order.  Samples that are not finite or >= 2^30 go to a
 // float side accumulator (NaN / Inf propagate like in the reference).  HBM traffic is unchanged: one 16-byte
 // store per pixel per launch.
@@ -91,8 +90,9 @@ __global__ void __launch_bounds__(BS, MB) render_sorted(const __grid_constant__ 
     float4* stB = stA + kSPool;                     // d.xyz, time
     float4* stC = stB + kSPool;                     // beta.xyz, prim
     uint4* stD = reinterpret_cast<uint4*>(stC + kSPool);  // item, global pixel index, sample, bounce | pixel slot << 16
-    unsigned long long* fx = reinterpret_cast<unsigned long long*>(stD + kSPool);  // [3][kSPix] fixed-point sums
-    float* fl = reinterpret_cast<float*>(fx + 3 * kSPix);                           // [3][kSPix] side sums
+    unsigned int* fxlo = reinterpret_cast<unsigned int*>(stD + kSPool);  // [3][kSPix] fixed-point sums, low words
+    unsigned int* fxhi = fxlo + 3 * kSPix;                               //                                high words
+    float* fl = reinterpret_cast<float*>(fxhi + 3 * kSPix);              // [3][kSPix] side sums
     unsigned int* prays = reinterpret_cast<unsigned int*>(fl + 3 * kSPix);          // [kSPix] color() invocations per pixel
     volatile uint16_t* queue = reinterpret_cast<volatile uint16_t*>(prays + kSPix);  // [C_QUEUES][kQCap]
     SortedCtl* ctl = reinterpret_cast<SortedCtl*>(const_cast<uint16_t*>(queue) + C_QUEUES * kQCap);
@@ -118,7 +118,7 @@ __global__ void __launch_bounds__(BS, MB) render_sorted(const __grid_constant__ 
         }
     };
 
-    for (int k = tid; k < 3 * kSPix; k += BS) fx[k] = 0ull, fl[k] = 0.0f;
+    for (int k = tid; k < 3 * kSPix; k += BS) fxlo[k] = 0u, fxhi[k] = 0u, fl[k] = 0.0f;
     for (int k = tid; k < kSPix; k += BS) prays[k] = 0u;
     for (int k = tid; k < C_QUEUES * kQCap; k += BS) queue[k] = kQEmpty;
     __syncthreads();
@@ -211,10 +211,18 @@ __global__ void __launch_bounds__(BS, MB) render_sorted(const __grid_constant__ 
                             // below 8192 a pixel's 2^23 samples cannot overflow the 64-bit sum; fireflies up to 2^30 take the
                             // same (exact, commutative) integer path — it would take > 448 of them at 1e9 in ONE pixel of one
                             // launch to wrap; only samples >= 2^30 or not finite go to the float side sum
-                            if (fabsf(v[ch]) < 1073741824.0f)
-                                atomicAdd(fx + ch * kSPix + pix, (unsigned long long)__float2ll_rn(v[ch] * 16777216.0f));
-                            else
+                            if (fabsf(v[ch]) < 1073741824.0f) {
+                                // two native 32-bit ATOMS.ADD instead of a 64-bit CAS loop: the carry out of the low word (and a
+                                // sample >= 256) goes to the high word; integer adds commute, so the sum stays exact and order-free
+                                const long long fx = __float2ll_rn(v[ch] * 16777216.0f);
+                                const unsigned int lo = (unsigned int)fx;
+                                unsigned int hi = (unsigned int)((unsigned long long)fx >> 32);
+                                const unsigned int old = atomicAdd(fxlo + ch * kSPix + pix, lo);
+                                hi += (old + lo < old) ? 1u : 0u;
+                                if (hi) atomicAdd(fxhi + ch * kSPix + pix, hi);
+                            } else {
                                 atomicAdd(fl + ch * kSPix + pix, v[ch]);
+                            }
                         }
                     }
                 }
@@ -273,7 +281,11 @@ __global__ void __launch_bounds__(BS, MB) render_sorted(const __grid_constant__ 
                 else atomicSub(&ctl->live, __popc(same));
             }
             pos = __shfl_sync(vmask, pos, leader);
-            if (ncls != C_DEAD) queue[ncls * kQCap + ((pos + __popc(same & ((1u << lane) - 1u))) & (kQCap - 1))] = (uint16_t)slot;
+            if (ncls != C_DEAD) {
+                volatile uint16_t* q = queue + ncls * kQCap + ((pos + __popc(same & ((1u << lane) - 1u))) & (kQCap - 1));
+                while (*q != kQEmpty) {}  // claimed one lap ago by a consumer that has not read it yet (header comment)
+                *q = (uint16_t)slot;
+            }
         }
     }
     __syncthreads();
@@ -288,9 +300,9 @@ __global__ void __launch_bounds__(BS, MB) render_sorted(const __grid_constant__ 
         slot_pixel((uint32_t)p, pi, pj);
         const size_t idx = (size_t)pj * rp.nx + pi;
         float4 out;
-        out.x = (float)((double)(long long)fx[p] * (1.0 / 16777216.0)) + fl[p];
-        out.y = (float)((double)(long long)fx[kSPix + p] * (1.0 / 16777216.0)) + fl[kSPix + p];
-        out.z = (float)((double)(long long)fx[2 * kSPix + p] * (1.0 / 16777216.0)) + fl[2 * kSPix + p];
+        out.x = (float)((double)(long long)(((unsigned long long)fxhi[p] << 32) | fxlo[p]) * (1.0 / 16777216.0)) + fl[p];
+        out.y = (float)((double)(long long)(((unsigned long long)fxhi[kSPix + p] << 32) | fxlo[kSPix + p]) * (1.0 / 16777216.0)) + fl[kSPix + p];
+        out.z = (float)((double)(long long)(((unsigned long long)fxhi[2 * kSPix + p] << 32) | fxlo[2 * kSPix + p]) * (1.0 / 16777216.0)) + fl[2 * kSPix + p];
         out.w = (float)rp.spp_count;
         if (rp.flags & RTW_FLAG_ACCUMULATE) {
             const float4 prev = accum[idx];
