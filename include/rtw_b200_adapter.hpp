@@ -214,6 +214,11 @@ struct render_options {
     uint64_t seed = 0;
     uint32_t flags = 0;
     rtw_render_stats* stats = nullptr;
+    // multi-GPU (one process or thread per GPU, include/rtw_b200.h section 4): every rank calls render() with the same
+    // scene and `spp` = ALL samples; rank r renders its share, the sums are reduced onto `root` (ncclReduce), and only the
+    // root's canvas is filled — the others come back empty.  nullptr = single GPU.
+    rtw_comm* comm = nullptr;
+    int root = 0;
 };
 
 // Drop-in for RayTracingWeekend.cpp:211-250: fills `canvas[j*nx+i]` with the gamma-2, clamped colour.
@@ -237,10 +242,19 @@ inline void render(scene& s, int nx, int ny, int spp, int max_depth, std::vector
     rtw_render_params p{};
     p.nx = nx, p.ny = ny, p.spp_begin = opt.spp_begin, p.spp_count = spp, p.max_depth = max_depth;
     p.flags = opt.flags, p.seed = opt.seed;
-    std::vector<float> accum((size_t)4 * nx * ny);
+    const bool is_root = !opt.comm || rtw_comm_rank(opt.comm) == opt.root;
+    std::vector<float> accum(is_root ? (size_t)4 * nx * ny : 0);
     rtw_render_stats st{};
-    if (rtw_render(g.sc, &p, accum.data(), &st) != RTW_OK) detail::walker::fail("render");
+    if (opt.comm) {
+        if (rtw_render_sharded(g.sc, opt.comm, &p, opt.root, is_root ? accum.data() : nullptr, &st) != RTW_OK) detail::walker::fail("render_sharded");
+    } else if (rtw_render(g.sc, &p, accum.data(), &st) != RTW_OK) {
+        detail::walker::fail("render");
+    }
     if (opt.stats) *opt.stats = st;
+    if (!is_root) {  // :241-250 happen on the root only
+        canvas.clear();
+        return;
+    }
     std::vector<double> rgb((size_t)3 * nx * ny);
     if (rtw_tonemap(accum.data(), nx, ny, rgb.data()) != RTW_OK) detail::walker::fail("tonemap");
     canvas.resize((size_t)nx * ny);
