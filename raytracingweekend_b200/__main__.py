@@ -30,6 +30,8 @@ def main(argv=None) -> int:
     ap.add_argument("--pipeline", default="megakernel", choices=["megakernel", "wavefront", "auto"])
     ap.add_argument("--debug-ray", action="store_true", help="RayTracingWeekend.cpp:221-225: every sample aims at the centre pixel")
     ap.add_argument("--normals", action="store_true", help="RenderType::Normal (RayTracingWeekend.cpp:135-136)")
+    ap.add_argument("--earth", default=None, metavar="JPEG", help="baseline JPEG for the image_texture scenes, decoded by rtw_decode_jpeg "
+                    "(e.g. the reference's RayTracingWeekend/earth.jpg); default: the packaged texels of that file")
     a = ap.parse_args(argv)
 
     rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
@@ -38,7 +40,7 @@ def main(argv=None) -> int:
         flags |= _lib.RTW_FLAG_DEBUG_RAY
     if a.normals:
         from . import Builder, load_earth
-        earth = load_earth() if a.scene in ("two_perlin_spheres_earth", "book2_final_scene") else None
+        earth = load_earth(a.earth) if a.scene in ("two_perlin_spheres_earth", "book2_final_scene") else None
         b = Builder().named_scene(a.scene, a.nx / a.ny, earth)
         b.set_render_type(1)
         scene = Scene(b, device=local)

@@ -16,7 +16,7 @@ import numpy as np
 from . import _lib
 from ._lib import RenderParams, RenderStats, check
 
-GOLDEN_EARTH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests", "golden", "earth_256x256_rgb8.bin")
+EARTH_TEXELS = os.path.join(os.path.dirname(os.path.abspath(__file__)), "data", "earth_256x256_rgb8.bin")
 
 SCENE_NAMES = ("light_sample", "dielectric_scene", "random_balls_scene", "cornell_box_scene", "cornell_box_aluminum",
                "two_perlin_spheres_earth", "book2_final_scene", "cornell_smoke_scene", "checker_spheres_scene", "cornell_two_boxes",
@@ -137,9 +137,15 @@ class Builder:
         return buf.raw
 
 
-def load_earth() -> np.ndarray:
-    """The 256x256 RGB8 texels of the reference's earth.jpg (decoded once by tests/golden/make_golden.py)."""
-    return np.fromfile(GOLDEN_EARTH, dtype=np.uint8).reshape(256, 256, 3)
+def load_earth(path: Optional[str] = None) -> np.ndarray:
+    """RGB8 texels for image_texture (texture.h:73-99 takes caller-decoded bytes; the reference ships earth.jpg but no loader).
+    `path`: a baseline JPEG, decoded by this library's own rtw_decode_jpeg (e.g. the reference's RayTracingWeekend/earth.jpg);
+    None: the packaged 256x256 texels of that file (data/earth_256x256_rgb8.bin — byte-identical to decoding it, pinned by
+    tests/test_imageio.py), so that the cfg2 / cfg3 scenes render where the reference tree is absent."""
+    if path is not None:
+        with open(path, "rb") as f:
+            return decode_jpeg(f.read())
+    return np.fromfile(EARTH_TEXELS, dtype=np.uint8).reshape(256, 256, 3)
 
 
 class Scene:

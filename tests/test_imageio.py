@@ -107,6 +107,7 @@ def test_earth_jpg_decodes_to_the_pinned_texels():
     assert tex.shape == (256, 256, 3)
     assert hashlib.sha256(tex.tobytes()).hexdigest() == "da3cdb69263fdf2cf28811cab55d915e2ed89ad1a492d35f11e6087513f87e39"
     assert np.array_equal(tex.ravel(), np.fromfile(os.path.join(GOLDEN, "earth_256x256_rgb8.bin"), dtype=np.uint8))
+    assert np.array_equal(tex, rtw.load_earth()) and np.array_equal(tex, rtw.load_earth(path))  # packaged texels == own decode
 
 
 def test_png_and_binary_ppm_hold_the_same_pixels_as_the_ascii_ppm(tmp_path):
