@@ -734,7 +734,24 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
             d.type = RTW_ITEM_BVH;
             d.first = d.end = pseudo_root(build_tree(objs, 1, true));
         } else {
+            const size_t rec0 = recs.size();
             add_groups(it.first, it.count, d.first, d.end);
+            // constant_medium boundaries (hittable.h:438-449) take the FP32 sphere test whatever their radius: the two boundary
+            // roots only clip the free-flight interval (an error of a few 1e-4 on a chord of 1e4 moves the scatter decision with
+            // probability ~1e-7), the boundary's normal is never used (:469-472), and rtw_intersect_batch skips media — while
+            // the FP64 test of the r = 5000 fog sphere ran twice per ray of the Book-2 final scene (442 M FP64 instructions per
+            // 32-spp frame, profiles/r1_sorted_v9_book2_final_ncu_details.txt).  RTW_MEDIUM_FP64=1 restores it (A/B).
+            static const bool medium_fp64 = [] { const char* v = getenv("RTW_MEDIUM_FP64"); return v && atoi(v) != 0; }();
+            if (it.type == RTW_ITEM_MEDIUM && !medium_fp64)
+                for (size_t r = rec0; r < recs.size(); r++) {
+                    int id;
+                    memcpy(&id, &recs[r].b.w, 4);
+                    if (id & REC_PRECISE) {
+                        id &= ~REC_PRECISE;
+                        memcpy(&recs[r].b.w, &id, 4);
+                        recs[r].b.x = 0.0f;
+                    }
+                }
         }
         if (it.type == RTW_ITEM_MEDIUM) feat |= F_MEDIA;
         items[i] = d;
