@@ -270,7 +270,13 @@ enum { /* rtw_render_params.flags */
     RTW_FLAG_AUTO = 1u << 3         /* let the backend pick megakernel or wavefront from the scene's features: the wavefront
                                        pipeline where shading is heavy and divergent (Perlin noise textures; bvh_node trees
                                        together with media) — the ncu evidence is in profiles/ — the megakernel otherwise.  Sums are then only
-                                       reproducible up to the order of float adds. */
+                                       reproducible up to the order of float adds. */,
+    RTW_FLAG_NEE = 1u << 4          /* OPT-IN, changes the estimator of RayTracingWeekend.cpp:117-132 (the reference casts no occlusion
+                                       rays): next-event estimation — every lambertian hit casts a shadow ray at a point of the
+                                       emitting xz_rect lights of the lights list and continues with a cosine-sampled direction.
+                                       Same expected image, different (on Cornell-like scenes much lower) variance; runs in the
+                                       wavefront pipeline (generate / extend / shade / shadow kernels), implies RTW_FLAG_WAVEFRONT.
+                                       stats.rays still counts color() invocations only, not shadow rays. */
 };
 
 typedef struct rtw_render_params {

@@ -14,6 +14,7 @@ RTW_FLAG_WAVEFRONT = 1
 RTW_FLAG_AUTO = 8
 RTW_FLAG_ACCUMULATE = 2
 RTW_FLAG_DEBUG_RAY = 4
+RTW_FLAG_NEE = 16
 RTW_NOALLOC_MAX_POOL_SLOTS = 65536
 RTW_COMM_ID_BYTES = 128
 

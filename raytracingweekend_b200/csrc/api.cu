@@ -166,6 +166,7 @@ struct rtw_scene {
     bool prefer_wavefront = false;  // RTW_FLAG_AUTO: set at upload from what the scene's shading costs
     void* wf_scratch = nullptr;  // wavefront path pool + queues (lazy)
     uint32_t wf_slots = 0;
+    size_t wf_bytes = 0;
     unsigned long long* wf_host_flag = nullptr;  // pinned
     bool rendered = false;  // ev1 was recorded at least once
     void release() {
@@ -900,6 +901,7 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
         mats[i] = d;
     }
     std::vector<DevLight> lights(fs->n_lights);
+    int n_nee_lights = 0;
     for (int i = 0; i < fs->n_lights; i++) {
         const rtw_flat_light& l = fs->lights[i];
         DevLight d{};
@@ -908,6 +910,14 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
         if (l.type == RTW_LIGHT_XZ_RECT) {
             d.k = (float)l.v[4];
             d.area = (float)((l.v[1] - l.v[0]) * (l.v[3] - l.v[2]));  // hittable.h:217
+            // the NEE set (RTW_FLAG_NEE): lights whose shape is a world-space xz_rect of the scene with an emitting material
+            for (int p = 0; p < fs->n_prims && !d.pad; p++) {
+                const rtw_flat_prim& q = fs->prims[p];
+                if (q.type == RTW_PRIM_XZ_RECT && q.xf < 0 && q.v[0] == l.v[0] && q.v[1] == l.v[1] && q.v[2] == l.v[2] && q.v[3] == l.v[3] &&
+                    q.v[4] == l.v[4] && q.material >= 0 && fs->materials[q.material].type == RTW_MAT_DIFFUSE_LIGHT)
+                    d.pad = 1;
+            }
+            n_nee_lights += d.pad;
         }
         lights[i] = d;
     }
@@ -1007,6 +1017,7 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
     d.n_world_items = fs->n_world_items, d.n_items = fs->n_items, d.n_prims = fs->n_prims, d.n_lights = fs->n_lights;
     d.render_type = fs->render_type, d.background_type = fs->background_type;
     d.features = feat, d.stack_exact = stack_exact, d.stack_render = stack_render, d.bvh4_stack = stack4_need;
+    d.n_nee_lights = n_nee_lights;
     d.n_bvh_items = 0;
     for (int i = 0; i < fs->n_world_items; i++) d.n_bvh_items += items[i].type == RTW_ITEM_BVH;
     // RTW_FLAG_AUTO: the multi-kernel wavefront pipeline beat the lane-owns-a-path megakernel on noise-textured and on
@@ -1079,7 +1090,8 @@ extern "C" int rtw_render_device(rtw_scene* s, const rtw_render_params* p, float
     if ((e = cudaMemsetAsync(s->d_counter, 0, 2 * sizeof(unsigned long long), st)) != cudaSuccess) return cuda_fail(e, "memset");
     if ((e = cudaEventRecord(s->ev0, st)) != cudaSuccess) return cuda_fail(e, "event");
     int launches = 1;
-    bool wavefront = (p->flags & RTW_FLAG_WAVEFRONT) != 0;
+    const bool nee = (p->flags & RTW_FLAG_NEE) != 0;  // the shadow stage lives in the wavefront pipeline
+    bool wavefront = (p->flags & RTW_FLAG_WAVEFRONT) != 0 || nee;
     if ((p->flags & RTW_FLAG_AUTO) && !wavefront) {
         // measured on B200 (profiles/README.md): the sorted shade kernel pays off when part of each warp would evaluate
         // 7-octave Perlin turbulence, or walk big trees and media together; Cornell-class scenes (constant or checker
@@ -1098,11 +1110,13 @@ extern "C" int rtw_render_device(rtw_scene* s, const rtw_render_params* p, float
         if (want > paths) want = paths;
         want = (want + 255) & ~255ull;
         if (want < 256) want = 256;
-        if ((uint32_t)want != s->wf_slots) {
+        const size_t want_bytes = wavefront_scratch_bytes((uint32_t)want, nee);
+        if ((uint32_t)want != s->wf_slots || want_bytes > s->wf_bytes) {
+            if (s->wf_scratch) cudaStreamSynchronize(st);  // a previous render on this stream may still use it
             dev_free(s->wf_scratch);
-            s->wf_scratch = nullptr, s->wf_slots = 0;
-            if ((e = dev_alloc((void**)&s->wf_scratch, wavefront_scratch_bytes((uint32_t)want))) != cudaSuccess) return cuda_fail(e, "cudaMalloc wavefront pool");
-            s->wf_slots = (uint32_t)want;
+            s->wf_scratch = nullptr, s->wf_slots = 0, s->wf_bytes = 0;
+            if ((e = dev_alloc((void**)&s->wf_scratch, want_bytes)) != cudaSuccess) return cuda_fail(e, "cudaMalloc wavefront pool");
+            s->wf_slots = (uint32_t)want, s->wf_bytes = want_bytes;
         }
         if (!s->wf_host_flag && (e = cudaMallocHost((void**)&s->wf_host_flag, 16)) != cudaSuccess) return cuda_fail(e, "cudaMallocHost");
         if ((e = launch_wavefront(s->dev, rp, (float4*)accum_dev, s->d_counter, s->wf_scratch, s->wf_slots, s->wf_host_flag, &launches, st)) !=
@@ -1192,6 +1206,10 @@ extern "C" int rtw_render_device_noalloc(rtw_scene* s, const rtw_render_params* 
     if (pool_slots > max_slots) {
         set_error("render_device_noalloc: pool_slots = " + std::to_string(pool_slots) + " exceeds RTW_NOALLOC_MAX_POOL_SLOTS = " +
                   std::to_string(max_slots) + " (the static device scratch holds no more; use rtw_render_device for bigger pools)");
+        return RTW_ERR_INVALID;
+    }
+    if (p->flags & RTW_FLAG_NEE) {
+        set_error("render_device_noalloc: RTW_FLAG_NEE needs the shadow-ray queue, which the static scratch does not hold");
         return RTW_ERR_INVALID;
     }
     if (p->max_depth > 255 || (long long)p->spp_begin + p->spp_count >= (1 << 24)) {

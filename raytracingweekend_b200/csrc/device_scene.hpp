@@ -113,7 +113,7 @@ struct DevTex {
 struct DevLight {
     float a0, a1, a2, a3;  // xz_rect: x0 x1 z0 z1; sphere: cx cy cz r
     float k, area;         // xz_rect
-    int32_t type, pad;
+    int32_t type, pad;     // pad = 1: an xz_rect light whose material is a diffuse_light (the NEE set)
 };
 
 struct DevCamera {
@@ -149,6 +149,7 @@ struct DevScene {
     int32_t stack_render;   // binary render trees walked in one loop, ENTER markers included (bvh_hit_items)
     int32_t bvh4_stack;     // 4-wide render trees: most references ever pushed at once
     int32_t n_bvh_items;    // tree items among the world items
+    int32_t n_nee_lights;   // emitting xz_rect lights of the lights list (DevLight.pad = 1): what RTW_FLAG_NEE samples
     DevCamera cam;
 };
 

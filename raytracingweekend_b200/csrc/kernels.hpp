@@ -24,7 +24,7 @@ cudaError_t launch_intersect(const DevScene& sc, const rtw_ray* rays, rtw_hit* h
 // Wavefront pipeline (wavefront.cu): generate / extend / shade kernels over a pool of `n_slots` path slots in `scratch`
 // (wavefront_scratch_bytes(n_slots) bytes of device memory).  Synchronises the stream between chunks of iterations to
 // poll the dead-slot counter through `host_flag` (pinned host memory, >= 8 bytes).
-size_t wavefront_scratch_bytes(uint32_t n_slots);
+size_t wavefront_scratch_bytes(uint32_t n_slots, bool nee = false);  // nee: + the shadow-ray queue of RTW_FLAG_NEE
 cudaError_t launch_wavefront(const DevScene& sc, const DevRenderParams& rp, float4* accum, unsigned long long* ray_counter,
                              void* scratch, uint32_t n_slots, unsigned long long* host_flag, int* launches_out, cudaStream_t st);
 

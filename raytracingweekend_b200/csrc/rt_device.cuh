@@ -169,7 +169,7 @@ RTW_DEV DevLight ld_light(const SceneView& sv, uint32_t off) {
     float4 a = hot4<SM>(sv, off), b = hot4<SM>(sv, off + 16);
     DevLight l;
     l.a0 = a.x, l.a1 = a.y, l.a2 = a.z, l.a3 = a.w;
-    l.k = b.x, l.area = b.y, l.type = fi(b.z), l.pad = 0;
+    l.k = b.x, l.area = b.y, l.type = fi(b.z), l.pad = fi(b.w);
     return l;
 }
 template <int SM>

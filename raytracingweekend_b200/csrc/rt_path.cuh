@@ -117,6 +117,77 @@ RTW_DEV bool shade_hit(const DevScene& sc, const SceneView& sv, const Rng& rng, 
     }
 }
 
+// ------------------------------------------------------------------------------------------------ next-event estimation
+// OPT-IN estimator (RTW_FLAG_NEE, wavefront pipeline only): changes RayTracingWeekend.cpp:117-132 — the
+// reference draws ONE direction from the 50/50 mixture of the cosine lobe and the lights list and never casts an occlusion
+// ray.  Here a lambertian hit (a) casts a SHADOW ray at a uniformly chosen point of the emitting xz_rect lights of the lights
+// list and, if it arrives, adds  beta * albedo * (cos/pi) * Le / pdf_light  to the pixel, and (b) continues with a
+// cosine-sampled direction (weight = albedo); a path that then runs into one of those lights by itself must not count its
+// emission again (`skip_emit`), while emission reached through a specular bounce, from emitters outside the lights list, or
+// seen by the camera is counted as before.  Same expectation as the reference's estimator, different variance.
+constexpr uint32_t SITE_NEE = 0x100u;  // Philox draw site of the light sample (the medium sites are SITE_MEDIUM0 + index)
+
+struct ShadowRay {
+    V3 o, d, w;  // origin, direction to the light sample (not normalised), weight = beta * albedo * cos / (pi * pdf)
+    bool cast;
+};
+
+// Emitting rect lights of the lights list = the set NEE samples.  Index of `prim` in it, or -1 (world-space xz_rects only).
+template <int SM>
+RTW_DEV bool nee_samples_prim(const DevScene& sc, const SceneView& sv, int prim, uint32_t pm) {
+    if (prim < 0 || (int)(pm & PM_TYPE_MASK) != RTW_PRIM_XZ_RECT || ((pm >> PM_XF_SHIFT) & PM_XF_MASK)) return false;
+    const float4 pa = cold4<SM>(sv, sc.off[SEC_PA] + (uint32_t)prim * 16u);
+    const float k = __uint_as_float(cold1<SM>(sv, sc.off[SEC_PB] + (uint32_t)prim * 16u));
+    for (int i = 0; i < sc.n_lights; i++) {
+        const DevLight l = ld_light<SM>(sv, sc.off[SEC_LIGHTS] + (uint32_t)i * 32u);
+        if (l.type == RTW_LIGHT_XZ_RECT && l.a0 == pa.x && l.a1 == pa.y && l.a2 == pa.z && l.a3 == pa.w && l.k == k) return true;
+    }
+    return false;
+}
+RTW_DEV int nee_light_count(const DevScene& sc) { return sc.n_nee_lights; }
+
+// Lambertian hit under NEE: fills the shadow ray, replaces `ray` by the cosine-sampled continuation and updates beta.
+template <uint32_t F, int SM>
+RTW_DEV void shade_lambert_nee(const DevScene& sc, const SceneView& sv, const Rng& rng, uint32_t bounce, const HitId& h, Ray& ray, V3& beta,
+                               ShadowRay& sh) {
+    const U4 rmain = rng.draw(bounce, SITE_MAIN), rl = rng.draw(bounce, SITE_NEE);
+    uint32_t pm;
+    const int mat_idx = hit_material<SM>(sc, sv, h, pm);
+    const DevMat m = ld_mat<SM>(sv, sc.off[SEC_MATS] + (uint32_t)mat_idx * 32u);
+    const bool need_uv = (F & F_TEXTURES) && !m.tex_is_constant;
+    const HitRec rec = complete_hit<F, SM>(sc, sv, h, pm, ray.o, ray.d, ray.time, need_uv);
+    const V3 att = material_texture<F, SM>(sc, sv, m, rec.u, rec.v, rec.p);
+    // (a) the light sample: the pick-th emitting rect of the lights list, a uniform point on it (hittable.h:224-228)
+    sh.cast = false;
+    const int nl = sc.n_nee_lights;
+    int pick = min(nl - 1, (int)((float)nl * rl.x));
+    float pdf = 0.0f;
+    V3 dir = mk(0.0f, 0.0f, 0.0f);
+    const uint32_t l0 = sc.off[SEC_LIGHTS];
+    for (int i = 0, seen = 0; i < sc.n_lights; i++) {  // the pick
+        const DevLight l = ld_light<SM>(sv, l0 + (uint32_t)i * 32u);
+        if (l.type != RTW_LIGHT_XZ_RECT || !l.pad) continue;  // pad = 1: the rect's material emits (set at upload)
+        if (seen++ == pick) dir = mk(fmaf(l.a1 - l.a0, rl.y, l.a0) - rec.p.x, l.k - rec.p.y, fmaf(l.a3 - l.a2, rl.z, l.a2) - rec.p.z);
+    }
+    const float len2 = dot(dir, dir), len = sqrtf(len2);
+    for (int i = 0; i < sc.n_lights; i++) {  // its density under "a uniformly picked emitting rect, a uniform point on it"
+        const DevLight l = ld_light<SM>(sv, l0 + (uint32_t)i * 32u);
+        if (l.type == RTW_LIGHT_XZ_RECT && l.pad) pdf += light_rect_pdf(l, rec.p, dir, len2, len);
+    }
+    pdf *= 1.0f / (float)nl;
+    const float cos_x = dot(rec.n, dir) * rcp_fast(len);
+    if (pdf > 0.0f && cos_x > 0.0f) {
+        sh.cast = true;
+        sh.o = rec.p, sh.d = dir;
+        sh.w = beta * att * (cos_x * rcp_fast(kPi * pdf));
+    }
+    // (b) the continuation: cosine lobe (pdf.h:26-29); scattering_pdf / pdf = 1, so the weight is the albedo
+    const V3 out = mixture_generate<SM>(sc, sv, rec.p, rec.n, U4{0.0f, rmain.y, rmain.z, rmain.w});
+    beta = beta * att;
+    ray.o = rec.p;
+    ray.d = out;
+}
+
 template <uint32_t F, int SM>
 RTW_DEV bool path_step(const DevScene& sc, const SceneView& sv, const Rng& rng, uint32_t bounce, Ray& ray, V3& beta, V3& L,
                        int* stack, int stride) {

@@ -38,7 +38,11 @@ struct WfParams {
     unsigned long long total_items;  // tiles * 32 * spp_count
     uint32_t n_slots;
     uint32_t tiles_x, n_tile_pixels;  // padded pixel count = tiles * 32
+    // RTW_FLAG_NEE: shadow rays of this iteration (o.xyz, time) (d.xyz, pixel) (weight.rgb, bounce | sample << 8); null = off
+    float4 *S0, *S1, *S2;
+    uint32_t* n_shadow;
 };
+constexpr uint32_t kSkipEmit = 0x80000000u;  // sign bit of the slot's ray time (>= 0): the next emitter hit was already sampled (NEE)
 
 // Work item -> (pixel, sample) -> camera ray; writes the slot.  Lanes that find no work mark the slot dead.
 // Called with any subset of lanes: the allocation is warp-aggregated over the calling lanes.
@@ -96,6 +100,7 @@ __global__ void __launch_bounds__(kWfBlock) wf_extend(const __grid_constant__ De
     const SceneView sv = stage_scene<SM>(sc, smem);
     int* stack = stack_base(sc, SM, smem) + threadIdx.x;
     uint32_t* counts = wp.counts + parity * kWfClasses;
+    if (wp.n_shadow && blockIdx.x == 0 && threadIdx.x == 0) *wp.n_shadow = 0;  // consumed by the previous iteration's wf_shadow
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     __shared__ uint32_t s_warp_count[kWfClasses][kWfBlock / 32];  // per class: lanes of each warp in this round
     __shared__ uint32_t s_base[kWfClasses][kWfBlock / 32];        // per class: queue position of each warp's first entry
@@ -113,7 +118,7 @@ __global__ void __launch_bounds__(kWfBlock) wf_extend(const __grid_constant__ De
                 rng.pixel = pixel, rng.sample = sb >> 8, rng.rk = rp.rk;
                 const uint32_t bounce = (sb & 0xffu) + 1u;
                 // :52 world.hit(r, 0.001f, DBL_MAX, rec)
-                const HitId h = closest_hit<F, SM, false>(sc, sv, mk(a.x, a.y, a.z), mk(b.x, b.y, b.z), a.w, 0.001f, FLT_MAX, &rng,
+                const HitId h = closest_hit<F, SM, false>(sc, sv, mk(a.x, a.y, a.z), mk(b.x, b.y, b.z), fabsf(a.w), 0.001f, FLT_MAX, &rng,
                                                           bounce, stack, kWfBlock);
                 wp.D[slot] = make_float4(h.t, __int_as_float(h.prim), __int_as_float(h.item), 0.0f);
                 rays++;
@@ -180,13 +185,31 @@ __global__ void __launch_bounds__(kWfBlock) wf_shade(const __grid_constant__ Dev
         rng.pixel = pixel, rng.sample = sb >> 8, rng.rk = rp.rk;
         const uint32_t bounce = (sb & 0xffu) + 1u;
         Ray ray;
-        ray.o = mk(a.x, a.y, a.z), ray.d = mk(b.x, b.y, b.z), ray.time = a.w;
+        ray.o = mk(a.x, a.y, a.z), ray.d = mk(b.x, b.y, b.z), ray.time = fabsf(a.w);
         V3 beta = mk(cc.x, cc.y, cc.z), L = mk(0.0f, 0.0f, 0.0f);
         HitId h;
         h.t = d.x, h.prim = __float_as_int(d.y), h.item = __float_as_int(d.z);
-        bool alive = shade_hit<F, SM>(sc, sv, rng, bounce, h, ray, beta, L);
+        bool alive, skip_next = false;
+        const bool nee = wp.n_shadow != nullptr && sc.n_nee_lights > 0;
+        if (nee && c == RTW_MAT_LAMBERTIAN) {  // warp-uniform (c is the queue's class): rt_path.cuh shade_lambert_nee
+            ShadowRay sh;
+            shade_lambert_nee<F, SM>(sc, sv, rng, bounce, h, ray, beta, sh);
+            if (sh.cast) {
+                const uint32_t q = atomicAdd(wp.n_shadow, 1u);
+                wp.S0[q] = make_float4(sh.o.x, sh.o.y, sh.o.z, ray.time);
+                wp.S1[q] = make_float4(sh.d.x, sh.d.y, sh.d.z, b.w);
+                wp.S2[q] = make_float4(sh.w.x, sh.w.y, sh.w.z, __uint_as_float((sb & ~0xffu) | bounce));
+            }
+            alive = skip_next = true;
+        } else if (nee && c == RTW_MAT_DIFFUSE_LIGHT && (__float_as_uint(a.w) & kSkipEmit) &&
+                   nee_samples_prim<SM>(sc, sv, h.prim, cold1<SM>(sv, sc.off[SEC_PM] + (uint32_t)max(h.prim, 0) * 4u))) {
+            alive = false;  // this light's emission was counted by the shadow ray of the previous (lambertian) bounce
+        } else {
+            alive = shade_hit<F, SM>(sc, sv, rng, bounce, h, ray, beta, L);
+        }
         if (alive && (int)bounce >= rp.max_depth) alive = false;  // :47-48: the next color() returns 0
         if (alive) {
+            if (skip_next) ray.time = __uint_as_float(__float_as_uint(ray.time) | kSkipEmit);
             wp.A[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.time);
             wp.B[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, b.w);
             wp.C[slot] = make_float4(beta.x, beta.y, beta.z, __uint_as_float((sb & ~0xffu) | bounce));
@@ -195,6 +218,36 @@ __global__ void __launch_bounds__(kWfBlock) wf_shade(const __grid_constant__ Dev
             if (L.x != 0.0f || L.y != 0.0f || L.z != 0.0f) atomicAdd(&accum[pixel], make_float4(L.x, L.y, L.z, 0.0f));
             wf_start_path<F, SM>(sc, rp, wp, slot);
         }
+    }
+}
+
+// RTW_FLAG_NEE: the shadow rays of this iteration.  A shadow ray is an ordinary world.hit() (media on its way scatter it with
+// their usual probability, from Philox counters of their own: bounce + 0x8000); it delivers  weight * Le  when the first thing
+// it meets is one of the sampled lights, seen from its emitting side (material.h:238-244).
+template <uint32_t F, int SM>
+__global__ void __launch_bounds__(kWfBlock) wf_shadow(const __grid_constant__ DevScene sc, const __grid_constant__ DevRenderParams rp,
+                                                      const __grid_constant__ WfParams wp, float4* __restrict__ accum) {
+    extern __shared__ uint4 smem[];
+    const SceneView sv = stage_scene<SM>(sc, smem);
+    int* stack = stack_base(sc, SM, smem) + threadIdx.x;
+    const uint32_t n = *wp.n_shadow;
+    for (uint32_t q = blockIdx.x * kWfBlock + threadIdx.x; q < n; q += gridDim.x * kWfBlock) {
+        const float4 s0 = wp.S0[q], s1 = wp.S1[q], s2 = wp.S2[q];
+        const uint32_t pixel = __float_as_uint(s1.w), sb = __float_as_uint(s2.w);
+        Rng rng;
+        rng.pixel = pixel, rng.sample = sb >> 8, rng.rk = rp.rk;
+        const V3 o = mk(s0.x, s0.y, s0.z), dv = mk(s1.x, s1.y, s1.z);
+        const HitId h = closest_hit<F, SM, false>(sc, sv, o, dv, s0.w, 0.001f, FLT_MAX, &rng, (sb & 0xffu) + 0x8000u, stack, kWfBlock);
+        if (h.prim < 0) continue;
+        uint32_t pm;
+        const int mat_idx = hit_material<SM>(sc, sv, h, pm);
+        const DevMat m = ld_mat<SM>(sv, sc.off[SEC_MATS] + (uint32_t)mat_idx * 32u);
+        if (m.type != RTW_MAT_DIFFUSE_LIGHT || !nee_samples_prim<SM>(sc, sv, h.prim, pm)) continue;
+        const bool need_uv = (F & F_TEXTURES) && !m.tex_is_constant;
+        const HitRec rec = complete_hit<F, SM>(sc, sv, h, pm, o, dv, s0.w, need_uv);
+        if (!(dot(rec.n, dv) > 0.0f)) continue;  // one-sided emission (Q23)
+        const V3 le = material_texture<F, SM>(sc, sv, m, rec.u, rec.v, rec.p);
+        atomicAdd(&accum[pixel], make_float4(s2.x * le.x, s2.y * le.y, s2.z * le.z, 0.0f));
     }
 }
 
@@ -211,6 +264,7 @@ cudaError_t wf_run_t(const DevScene& sc, const DevRenderParams& rp, const WfPara
     if (smem > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(wf_extend<F, SM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(wf_shade<F, SM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(wf_shadow<F, SM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
     }
     if (generate) wf_generate<F, SM><<<grid, kWfBlock, 0, st>>>(sc, rp, wp);
@@ -218,6 +272,7 @@ cudaError_t wf_run_t(const DevScene& sc, const DevRenderParams& rp, const WfPara
         const int parity = (first_iteration + it) & 1;
         wf_extend<F, SM><<<grid, kWfBlock, smem, st>>>(sc, rp, wp, parity, ray_counter);
         wf_shade<F, SM><<<grid, kWfBlock, smem, st>>>(sc, rp, wp, parity, accum);
+        if (wp.n_shadow) wf_shadow<F, SM><<<grid, kWfBlock, smem, st>>>(sc, rp, wp, accum);
     }
     return cudaGetLastError();
 }
@@ -227,8 +282,8 @@ cudaError_t wf_run(const DevScene& sc, const DevRenderParams& rp, const WfParams
 }
 }  // namespace
 
-size_t wavefront_scratch_bytes(uint32_t n_slots) {
-    return (size_t)n_slots * (4 * sizeof(float4) + kWfClasses * sizeof(uint32_t)) + 256;
+size_t wavefront_scratch_bytes(uint32_t n_slots, bool nee) {
+    return (size_t)n_slots * ((nee ? 7 : 4) * sizeof(float4) + kWfClasses * sizeof(uint32_t)) + 256;
 }
 
 // Renders the whole sample range.  `scratch` holds wavefront_scratch_bytes(n_slots) bytes; `host_flag` is pinned host
@@ -246,6 +301,13 @@ cudaError_t launch_wavefront(const DevScene& sc, const DevRenderParams& rp, floa
     p = (uint8_t*)(((uintptr_t)p + 15) & ~(uintptr_t)15);
     wp.next_item = (unsigned long long*)p, p += 8;
     wp.dead = (unsigned long long*)p, p += 8;
+    if (rp.flags & RTW_FLAG_NEE) {  // scratch was sized with nee = true
+        wp.n_shadow = (uint32_t*)p, p += 16;
+        p = (uint8_t*)(((uintptr_t)p + 15) & ~(uintptr_t)15);
+        wp.S0 = (float4*)p, p += (size_t)n_slots * sizeof(float4);
+        wp.S1 = (float4*)p, p += (size_t)n_slots * sizeof(float4);
+        wp.S2 = (float4*)p, p += (size_t)n_slots * sizeof(float4);
+    }
     wp.n_slots = n_slots;
     wp.tiles_x = (uint32_t)((rp.nx + 7) / 8);
     const uint32_t tiles_y = (uint32_t)((rp.ny + 3) / 4);
@@ -269,7 +331,7 @@ cudaError_t launch_wavefront(const DevScene& sc, const DevRenderParams& rp, floa
     for (;;) {
         if ((e = wf_run(sc, rp, wp, accum, ray_counter, grid, chunk, iteration, iteration == 0, st)) != cudaSuccess) return e;
         iteration += chunk;
-        launches += 2 * chunk;
+        launches += (wp.n_shadow ? 3 : 2) * chunk;
         if ((e = cudaMemcpyAsync(host_flag, wp.dead, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st)) != cudaSuccess) return e;
         if ((e = cudaStreamSynchronize(st)) != cudaSuccess) return e;
         if (*host_flag >= (unsigned long long)n_slots) break;
@@ -316,7 +378,7 @@ uint32_t wavefront_noalloc_max_slots() { return kNoAllocMaxSlots; }
 // the polls land in a stack variable.  n_slots <= kNoAllocMaxSlots (checked by the caller, re-checked here).
 cudaError_t launch_wavefront_noalloc(const DevScene& sc, const DevRenderParams& rp, float4* accum, uint32_t n_slots,
                                      unsigned long long* rays_out, int* launches_out, cudaStream_t st) {
-    if (n_slots == 0 || n_slots > kNoAllocMaxSlots || wavefront_scratch_bytes(n_slots) > kNoAllocRayCounterOff) return cudaErrorInvalidValue;
+    if (n_slots == 0 || n_slots > kNoAllocMaxSlots || wavefront_scratch_bytes(n_slots, false) > kNoAllocRayCounterOff || (rp.flags & RTW_FLAG_NEE)) return cudaErrorInvalidValue;
     uint8_t* base = nullptr;
     cudaError_t e = noalloc_scratch_ptr(&base);
     if (e != cudaSuccess) return e;

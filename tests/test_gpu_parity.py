@@ -313,6 +313,49 @@ def test_converged_image_vs_reference_render(scenes, scene):
     assert np.allclose(gm[ok].mean(axis=0), rm[ok].mean(axis=0), rtol=0.03, atol=2e-3)
 
 
+@pytest.mark.parametrize("scene", ["cornell_box_aluminum", "cornell_two_boxes", "book2_final_scene"])
+def test_nee_flag_converges_to_the_reference_image(scenes, scene):
+    """RTW_FLAG_NEE (opt-in next-event estimation with shadow rays, the wavefront pipeline's shadow stage) changes the
+    estimator of RayTracingWeekend.cpp:117-132 but not its expectation: the converged image must pass the SAME test against
+    the unmodified reference's CPU render as the default estimator does (tier 3b: per-pixel z-test, channel means), and agree
+    with the default estimator's image; the per-pixel variance ratio of the two estimators is printed and recorded."""
+    NEE = rtw._lib.RTW_FLAG_NEE
+    g = np.load(os.path.join(GOLDEN, f"image_{scene}.npz"))
+    nx, ny, rspp = int(g["nx"]), int(g["ny"]), int(g["spp"])
+    b, sc = scenes(scene, nx / ny)
+    K, bspp = 8, 1024
+    nee = np.stack([sc.render(nx, ny, bspp, seed=300 + k, flags=NEE)[0][..., :3].astype(np.float64) / bspp for k in range(K)])
+    std = np.stack([sc.render(nx, ny, bspp, seed=400 + k)[0][..., :3].astype(np.float64) / bspp for k in range(K)])
+    acc, st = sc.render(nx, ny, 16, seed=1, flags=NEE)
+    assert st["kernel_launches"] > 3 and np.all(acc[..., 3] == 16)
+    nm, sm = nee.mean(axis=0), std.mean(axis=0)
+    nvar, svar = nee.var(axis=0, ddof=1) / K, std.var(axis=0, ddof=1) / K
+    rm = g["sum"] / rspp
+    rvar = np.maximum(g["sumsq"] / rspp - rm * rm, 0.0) / rspp
+    ok = np.isfinite(rm).all(axis=2) & np.isfinite(nm).all(axis=2) & np.isfinite(sm).all(axis=2)
+    assert ok.mean() > 0.999
+    z_ref = (np.abs(nm - rm) / np.sqrt(rvar + nvar + 1e-12))[ok]
+    z_std = (np.abs(nm - sm) / np.sqrt(svar + nvar + 1e-12))[ok]
+    ratio = float(np.mean(svar[ok]) / max(np.mean(nvar[ok]), 1e-30))
+    stats = {"scene": scene, "z_ref_gt4": float((z_ref > 4).mean()), "z_ref_median": float(np.median(z_ref)),
+             "z_std_gt4": float((z_std > 4).mean()), "z_std_median": float(np.median(z_std)),
+             "mean_nee": [float(x) for x in nm[ok].mean(axis=0)], "mean_ref": [float(x) for x in rm[ok].mean(axis=0)],
+             "variance_ratio_default_over_nee": ratio}
+    print(stats)
+    ol.record_stats("nee", stats)
+    assert (z_ref > 4).mean() < 0.005 and np.median(z_ref) < 1.0, stats
+    assert (z_std > 4).mean() < 0.005 and np.median(z_std) < 1.0, stats
+    assert np.allclose(nm[ok].mean(axis=0), rm[ok].mean(axis=0), rtol=0.03, atol=2e-3), stats
+
+
+def test_nee_flag_without_emitting_rect_lights_is_the_wavefront_render(scenes):
+    """No emitting xz_rect in the lights list (random_balls_scene has no lights at all): the flag changes nothing."""
+    b, sc = scenes("random_balls_scene", 1.5)
+    a, sa = sc.render(48, 32, 4, seed=3, flags=rtw._lib.RTW_FLAG_WAVEFRONT)
+    c, sc_ = sc.render(48, 32, 4, seed=3, flags=rtw._lib.RTW_FLAG_NEE)
+    assert sa["rays"] == sc_["rays"] and np.allclose(a, c, rtol=1e-4, atol=1e-4)
+
+
 def test_spp_shards_are_disjoint_streams_and_sum_exactly(scenes):
     """one GPU rendering G logical shards == one render of the whole range (per-pixel sums differ only
     by FP32 reassociation), shards are bit-reproducible, and the ACCUMULATE flag resumes a render."""
