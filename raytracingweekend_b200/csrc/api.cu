@@ -16,6 +16,7 @@
 
 #include "flat.hpp"
 #include "kernels.hpp"
+#include "lbvh.hpp"
 
 using namespace rtw;
 
@@ -680,6 +681,63 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
         nodes[idx] = d;
         return idx;
     };
+    // Device-side alternative (RTW_DEVICE_BVH=1, lbvh.cu): Morton codes, sort, Karras' radix tree and the box fit run on the GPU;
+    // the nodes come back as (left, right, box) and are written as DevNode records here, so padding, traversal, stack needs and
+    // the 4-wide collapse are those of the SAH build.  Leaves hold ONE object (a primitive, or a reference leaf).
+    static const bool device_bvh = [] { const char* v = getenv("RTW_DEVICE_BVH"); return v && atoi(v) != 0; }();
+    bool device_build_failed = false;
+    std::function<int(std::vector<Obj>&, bool)> build_tree_device = [&](std::vector<Obj>& objs, bool prims) -> int {
+        const int n = (int)objs.size();
+        std::vector<int> leaf_ref(n);
+        for (int i = 0; i < n; i++) {  // leaves first, in object (= list) order: the tie rule orders equal hits by leaf offset
+            if (!prims) {
+                leaf_ref[i] = ~objs[i].id;
+                continue;
+            }
+            std::vector<int> ids{objs[i].id};
+            int2 lf;
+            add_groups_of(ids, lf.x, lf.y);
+            leaves.push_back(lf);
+            leaf_box.push_back(padded(objs[i].box));
+            leaf_ref[i] = ~(int)(leaves.size() - 1);
+        }
+        if (n == 1) return leaf_ref[0];
+        std::vector<float> boxes((size_t)n * 6);
+        for (int i = 0; i < n; i++)
+            for (int k = 0; k < 3; k++) boxes[6 * i + k] = (float)objs[i].box.lo[k], boxes[6 * i + 3 + k] = (float)objs[i].box.hi[k];
+        std::vector<int> L, R;
+        std::vector<float> nb;
+        if (lbvh_build(boxes, L, R, nb) != cudaSuccess || (int)L.size() != n - 1) {
+            device_build_failed = true;
+            cudaGetLastError();
+            return leaf_ref[0];
+        }
+        const int base = (int)nodes.size();
+        nodes.resize(base + n - 1);
+        std::function<int(int, int)> depth_of = [&](int ref, int d) -> int {
+            if (ref < 0) return d;
+            return std::max(depth_of(L[ref], d + 1), depth_of(R[ref], d + 1));
+        };
+        max_depth = std::max(max_depth, depth_of(0, 1));
+        // boxes of the children live in the parent (DevNode); node boxes are unions of the padded leaf boxes, as in build_tree
+        std::function<Box(int)> box_of = [&](int ref) -> Box {
+            if (ref < 0) return leaf_box[~leaf_ref[~ref]];
+            Box b = box_of(L[ref]);
+            b.merge(box_of(R[ref]));
+            return b;
+        };
+        for (int i = 0; i < n - 1; i++) {
+            DevNode d{};
+            const int lref = L[i] < 0 ? leaf_ref[~L[i]] : base + L[i], rref = R[i] < 0 ? leaf_ref[~R[i]] : base + R[i];
+            Box lb = prims || L[i] >= 0 ? box_of(L[i]) : leaf_box[~leaf_ref[~L[i]]];
+            Box rb = prims || R[i] >= 0 ? box_of(R[i]) : leaf_box[~leaf_ref[~R[i]]];
+            set_child(d, false, &lb, lref);
+            set_child(d, true, &rb, rref);
+            nodes[base + i] = d;
+        }
+        (void)nb;  // the device's own boxes bound the UNPADDED objects; the render tree needs the padded leaf boxes (FP32 slab test)
+        return base;
+    };
     auto pseudo_root = [&](int root) {  // left child = the tree, right child empty
         DevNode pr{};
         Box rb = node_box(root);
@@ -726,14 +784,14 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
                     for (int p = 0; p < fs->leaves[l].prim_count; p++) o.box.merge(prim_box(fs->leaves[l].first_prim + p));
                     objs.push_back(o);
                 }
-                d.end = pseudo_root(build_tree(objs, 1, false));
+                d.end = pseudo_root(device_bvh ? build_tree_device(objs, false) : build_tree(objs, 1, false));
             }
         } else if (it.type == RTW_ITEM_PRIMS && list_bvh_min > 0 && it.count >= list_bvh_min) {
             feat |= F_BVH;
             std::vector<Obj> objs(it.count);
             for (int k = 0; k < it.count; k++) objs[k].id = it.first + k, objs[k].box = prim_box(it.first + k);
             d.type = RTW_ITEM_BVH;
-            d.first = d.end = pseudo_root(build_tree(objs, 1, true));
+            d.first = d.end = pseudo_root(device_bvh ? build_tree_device(objs, true) : build_tree(objs, 1, true));
         } else {
             const size_t rec0 = recs.size();
             add_groups(it.first, it.count, d.first, d.end);
@@ -859,6 +917,10 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
                 k++;
             }
         stack_render = std::max(stack_render, k);  // all markers are pushed before the first is popped
+    }
+    if (device_build_failed) {
+        set_error("scene_create: the device-side tree build (RTW_DEVICE_BVH=1) failed");
+        return nullptr;
     }
     if (getenv("RTW_DEBUG_TREES"))
         fprintf(stderr, "rtw trees: %zu binary nodes (depth %d; stack need: exact %d, render %d), %zu 4-wide nodes (stack need %d), %zu leaves\n",

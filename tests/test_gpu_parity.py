@@ -645,6 +645,30 @@ def test_upload_time_trees_do_not_change_hits_or_images():
     assert sa["rays"] == sc_["rays"] and np.array_equal(a, c)
 
 
+@pytest.mark.parametrize("scene,nx,ny,spp", [("random_balls_scene", 96, 64, 8), ("book2_final_scene", 64, 64, 8)])
+def test_device_side_tree_build_does_not_change_hits_or_images(scene, nx, ny, spp):
+    """RTW_DEVICE_BVH=1 (read at rtw_scene_create): the render trees are built on the GPU (csrc/lbvh.cu: Morton codes, bitonic
+    sort, Karras' radix tree, bottom-up fit) instead of by the host SAH builder.  Another tree, the same closest hits: renders
+    with the same Philox keys are bit-identical, ray counts equal, and world.hit() on a ray batch returns the same records."""
+    b = builder_for(scene, nx / ny)
+    host = rtw.Scene(b)
+    os.environ["RTW_DEVICE_BVH"] = "1"
+    try:
+        dev = rtw.Scene(b)
+    finally:
+        del os.environ["RTW_DEVICE_BVH"]
+    a, sa = host.render(nx, ny, spp, seed=3)
+    c, sc_ = dev.render(nx, ny, spp, seed=3)
+    assert sa["rays"] == sc_["rays"] and np.array_equal(a, c, equal_nan=True)
+    w, sw = dev.render(nx, ny, spp, seed=3, flags=rtw._lib.RTW_FLAG_WAVEFRONT)
+    assert sw["rays"] == sa["rays"]
+    rays = ol.fixed_rays(b, 1 << 16, 5).astype(np.float32)
+    hh, hd = host.intersect_batch(rays), dev.intersect_batch(rays)
+    assert np.array_equal(hh["prim"], hd["prim"]) and np.array_equal(hh["t"], hd["t"])
+    host.close()
+    dev.close()
+
+
 def test_auto_flag_picks_the_design_from_scene_features(scenes):
     """RTW_FLAG_AUTO = the design that measured fastest for the scene class.  With the material-sorted
     megakernel that is the megakernel for every class; the wavefront pipeline stays selectable with RTW_FLAG_WAVEFRONT."""
