@@ -801,6 +801,13 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
             // the FP64 test of the r = 5000 fog sphere ran twice per ray of the Book-2 final scene (442 M FP64 instructions per
             // 32-spp frame, profiles/r1_sorted_v9_book2_final_ncu_details.txt).  RTW_MEDIUM_FP64=1 restores it (A/B).
             static const bool medium_fp64 = [] { const char* v = getenv("RTW_MEDIUM_FP64"); return v && atoi(v) != 0; }();
+            // a medium whose boundary is exactly one (non-moving) sphere: remember the record, closest_hit takes both boundary
+            // roots from one quadratic (RTW_MEDIUM_ONE_SPHERE=0 switches this off: A/B)
+            static const bool one_sphere_on = [] { const char* v = getenv("RTW_MEDIUM_ONE_SPHERE"); return !v || atoi(v) != 0; }();
+            d.root4 = -1;
+            if (it.type == RTW_ITEM_MEDIUM && !medium_fp64 && one_sphere_on && it.count == 1 && fs->prims[it.first].type == RTW_PRIM_SPHERE &&
+                fs->prims[it.first].xf < 0 && recs.size() == rec0 + 1)
+                d.root4 = -2 - (int)rec0;  // record index, turned into a byte offset with the others below
             if (it.type == RTW_ITEM_MEDIUM && !medium_fp64)
                 for (size_t r = rec0; r < recs.size(); r++) {
                     int id;
@@ -1028,9 +1035,12 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
     }
     for (DevItem& d : items) {
         d.xf = xf_off(d.xf);
-        if (d.type == RTW_ITEM_BVH)
+        if (d.type == RTW_ITEM_BVH) {
             d.first = ref_off(d.first), d.end = ref_off(d.end), d.root4 = (int32_t)(off[SEC_NODES4] + (uint32_t)d.root4 * sizeof(DevNode4));
-        else d.first = group_off(d.first), d.end = group_off(d.end);
+        } else {
+            d.first = group_off(d.first), d.end = group_off(d.end);
+            d.root4 = (d.type == RTW_ITEM_MEDIUM && d.root4 <= -2) ? rec_off(-2 - d.root4) : -1;
+        }
     }
     for (DevNode& n : nodes) {
         int l, r;

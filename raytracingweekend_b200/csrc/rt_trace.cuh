@@ -363,8 +363,20 @@ RTW_DEV HitId closest_hit(const DevScene& sc, const SceneView& sv, V3 o, V3 d, f
             // the two boundary searches (:438-442, :445-449) share one call site (code size): pass 1 starts at
             // `rec1.t + 0.0001f` (:447); in FP32 that step can vanish for |t| > ~800, so advance at least one ulp
             bool both = false;
+            const int one_sphere = (int)hot1<SM>(sv, ia + 28u);  // DevItem.root4 of a medium: its boundary is ONE FP32 sphere record
+            if (one_sphere >= 0) {
+                // one quadratic gives both boundary hits, with the very numbers of the two searches below: the first search
+                // (from -inf) returns the near root, the second (from just behind it) can only return the far one
+                const float4 ra = hot4<SM>(sv, (uint32_t)one_sphere);
+                float r0, r1;
+                if (sphere_roots(lk.o - mk(ra.x, ra.y, ra.z), lk.d, lk.a, lk.inv_a, ra.w, r0, r1)) {
+                    const float from = fmaxf(r0 + 0.0001f, nextafterf(r0, FLT_MAX));
+                    both = (r0 > -FLT_MAX) & (r0 < FLT_MAX) & (r1 > from) & (r1 < FLT_MAX);
+                    t1 = r0, t2 = r1;
+                }
+            }
 #pragma unroll 1
-            for (int pass = 0; pass < 2; pass++) {
+            for (int pass = 0; pass < 2 && one_sphere < 0; pass++) {
                 float tb = FLT_MAX;
                 int pb = -1;
                 const float from = pass == 0 ? -FLT_MAX : fmaxf(t1 + 0.0001f, nextafterf(t1, FLT_MAX));
