@@ -18,7 +18,7 @@ LIB = os.path.join(HERE, "lib")
 OBJ = os.path.join(HERE, "build")
 
 HOST_SRCS = ["builder.cpp", "scenes.cpp", "hostio.cpp", "imageio.cpp"]
-CUDA_SRCS = ["kernels.cu", "sorted.cu", "wavefront.cu", "lbvh.cu", "api.cu"]
+CUDA_SRCS = ["kernels.cu", "sorted.cu", "sorted_big.cu", "wavefront.cu", "lbvh.cu", "api.cu"]
 NVCC_ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 CXXFLAGS = ["-std=c++17", "-O2", "-fPIC", "-Wall"]
 # FP32 division / sqrt as reciprocal-multiply and MUFU forms (2 ulp), denormals flushed; sin/cos/log/exp stay accurate

@@ -78,11 +78,20 @@ RTW_DEV uint4 philox4x32_10(uint4 c, const uint32_t* __restrict__ rk) {
     return c;
 }
 RTW_DEV float u01(uint32_t x) { return (float)(x >> 8) * 5.9604644775390625e-8f; }  // 2^-24
+// RTW_PHILOX_OOL (per translation unit): ONE out-of-line copy of the ten rounds instead of one inlined copy per draw site (six
+// sites x 57 instructions in the all-features kernels, which are bound by the SM instruction cache: DESIGN.md 4.6).
+#ifdef RTW_PHILOX_OOL
+static __device__ __noinline__ uint4 philox4x32_10_call(uint4 c, const uint32_t* __restrict__ rk) { return philox4x32_10(c, rk); }
+#endif
 struct Rng {
     uint32_t pixel, sample;
     const uint32_t* rk;  // DevRenderParams::rk of this launch
     RTW_DEV U4 draw(uint32_t bounce, uint32_t site) const {
+#ifdef RTW_PHILOX_OOL
+        uint4 r = philox4x32_10_call(make_uint4(pixel, sample, bounce, site), rk);
+#else
         uint4 r = philox4x32_10(make_uint4(pixel, sample, bounce, site), rk);
+#endif
         return U4{u01(r.x), u01(r.y), u01(r.z), u01(r.w)};
     }
 };

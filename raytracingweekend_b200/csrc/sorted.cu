@@ -1,362 +1,12 @@
-// sorted.cu — the megakernel with material-sorted shading (sm_100a).
-//
-// The lane-owns-a-path megakernel (kernels.cu) traverses at ~31 of 32 lanes but shades at 3-15: after the hit a warp
-// holds a mix of lambertian, dielectric, metal and terminal events and runs every branch.  Here the path state lives in
-// shared memory instead of registers, and the warps of a block exchange paths through per-class queues so that a
-// warp always shades 32 paths of ONE material class and then traces their 32 new rays:
-//
-//   block  = 256, 512 or 768 threads (per variant class, launch_sorted_t), one 16x16 pixel tile, one pool of (pixel, sample) items like the
-//            warp pool of kernels.cu
-//   slots  = kSPool path slots in shared memory, 64 B each: (o, t) (d, time) (beta, prim) (item, pixel, sample, bounce)
-//   queues = one ring of slot ids per class in shared memory {lambertian, dielectric, metal, isotropic, terminal
-//            (miss / emitter), needs-a-camera-ray}; producers reserve with one atomicAdd per (warp, class) found by
-//            match_any, consumers claim 32 entries with a CAS on the head.  No block-wide barrier after start-up.
-//   unit   = claim 32 entries of one class -> load state -> shade_hit (coherent) -> new ray -> closest_hit (full
-//            lanes) -> classify -> store state -> push.  Terminal units add their radiance and start 32 new camera
-//            rays on the spot, so camera maths also runs at full lanes.
-//
-// Rings: capacity >= number of slots.  A consumer reads (and clears) its entries right after the CAS that claimed them, and
-// a producer WAITS until its target position is empty before it writes (one LDS per push), so a delayed consumer can never
-// be overwritten: the worst a slow warp causes is a short producer spin, not a lost slot (round 1 relied on warp timing
-// here, and a variant that batched two claims hung).  Two producers that target the same position one lap apart may land
-// in either order — entries are only slot ids of one class, any order is correct.
-//
-// Per-pixel sums are 64-bit fixed point (2^-24) in shared memory (kept as two 32-bit words, see the adds): integer adds commute, so the image stays
-// bit-reproducible although units run in a timing-dependent order.  Samples that are not finite or >= 2^30 go to a
-// float side accumulator (NaN / Inf propagate like in the reference).  HBM traffic is unchanged: one 16-byte
-// store per pixel per launch.
-#include <cstdio>
-#include <cstdlib>
-
-#include "kernels.hpp"
-#include "rt_path.cuh"
-#include "rt_stage.cuh"
+// sorted.cu — instantiations and dispatch of the material-sorted megakernel (sorted_kernel.cuh).
+#include "sorted_kernel.cuh"
 
 namespace rtw {
 
-constexpr int kSBlock = 256;
-constexpr int kSTile = 16;  // 16 x 16 pixels per block
-constexpr int kSPix = kSTile * kSTile;
-// BS = threads per block, PT = path slots per 256 threads, MB = resident blocks per SM (launch bounds -> registers).
-// Measured choices (profiles/r1_ab_*.txt), set in launch_sorted_t.  The common thread: ONE big pool per SM shared by many
-// warps keeps the class queues full (whole 32-path units, few waits), as long as the registers suffice:
-//   Cornell-class variant (F_XF only):        512 threads, 1024 slots, 2 blocks/SM: 64 registers, issue-bound, wants 32
-//                                             warps per SM: 6.40 -> 6.53 Gpaths/s over 256 / 512 / 4 blocks; 1024 threads
-//                                             with 2048 slots in one block loses again (6.33);
-//   texture variant (Perlin, image, checker): 768 threads, 1536 slots, 1 block/SM, 85 registers: Perlin 7.41 -> 8.88,
-//                                             checker spheres 5.43 -> 7.53, light_sample 6.78 -> 10.2 over 256 threads /
-//                                             768 slots / 2 blocks (896 threads the same, 512 and 1024 threads less);
-//   BVH variants on unstaged scenes:          256 threads, 512 slots, 2 blocks/SM: 128 registers, no spills, and two 64 KB
-//                                             blocks leave ~100 KB of L1 for nodes and records (Book-2 final 0.485 -> 0.59;
-//                                             bigger pools or blocks lose: they eat the L1);
-//   all-features variant on staged scenes:    256 threads, 512 slots, 3 blocks/SM (Cornell smoke 4.14; 768 threads in one
-//                                             block the same, 512 threads 3.37, 2 blocks of 256 3.32).
-__host__ __device__ constexpr int pool_slots(int pt) { return 256 * pt; }
-__host__ __device__ constexpr int queue_cap(int pt) {  // ring capacity per class (power of two >= slots)
-    return pool_slots(pt) <= 512 ? 512 : (pool_slots(pt) <= 1024 ? 1024 : 2048);
+// spp * max_depth < 2^32: the per-pixel count of color() invocations is 32 bits
+bool sorted_supports(const DevRenderParams& rp) {
+    return rp.spp_count <= (1 << 23) && rp.max_depth < (1 << 16) && (unsigned long long)rp.spp_count * (unsigned long long)rp.max_depth < (1ull << 32);
 }
-__host__ __device__ constexpr int min_blocks(int pt) { return pt <= 2 ? 4 : (pt == 3 ? 3 : 2); }
-
-enum : int { C_LAMB = 0, C_DIEL, C_METAL, C_ISO, C_TERM, C_REGEN, C_QUEUES, C_DEAD = C_QUEUES };
-constexpr uint16_t kQEmpty = 0xffffu;
-
-#ifdef RTW_SORTED_STATS
-__device__ int g_stats[8][2];
-#endif
-struct SortedCtl {
-    unsigned int head[8], tail[8];  // per class ring: [head, tail) are queued entries (tail = reserved)
-    unsigned int item_next;         // the block's (pixel, sample) pool
-    int live;                       // slots that still carry or may get a path
-};
-
-constexpr size_t sorted_pool_bytes(int pt) {
-    return (size_t)pool_slots(pt) * 64 + (size_t)C_QUEUES * queue_cap(pt) * 2 + (size_t)kSPix * (3 * (8 + 4) + 4) + sizeof(SortedCtl) + 64;
-}
-
-// BS = threads per block (a multiple of 32; the pixel tile and the pool do not depend on it)
-template <uint32_t F, int SM, int PT, int MB, int BS>
-__global__ void __launch_bounds__(BS, MB) render_sorted(const __grid_constant__ DevScene sc,
-                                                                              const __grid_constant__ DevRenderParams rp,
-                                                                              float4* __restrict__ accum,
-                                                                              unsigned long long* __restrict__ ray_counter,
-                                                                              uint32_t pool_off) {
-    constexpr int kSPool = pool_slots(PT), kQCap = queue_cap(PT);
-    extern __shared__ uint4 smem[];
-    const SceneView sv = stage_scene<SM>(sc, smem);
-    int* stack = stack_base(sc, SM, smem) + threadIdx.x;
-    // pool carve-up (pool_off = staged bytes + stacks, 16-byte aligned by the host)
-    uint8_t* base = reinterpret_cast<uint8_t*>(smem) + pool_off;
-    float4* stA = reinterpret_cast<float4*>(base);  // o.xyz, t
-    float4* stB = stA + kSPool;                     // d.xyz, time
-    float4* stC = stB + kSPool;                     // beta.xyz, prim
-    uint4* stD = reinterpret_cast<uint4*>(stC + kSPool);  // item, global pixel index, sample, bounce | pixel slot << 16
-    unsigned int* fxlo = reinterpret_cast<unsigned int*>(stD + kSPool);  // [3][kSPix] fixed-point sums, low words
-    unsigned int* fxhi = fxlo + 3 * kSPix;                               //                                high words
-    float* fl = reinterpret_cast<float*>(fxhi + 3 * kSPix);              // [3][kSPix] side sums
-    unsigned int* prays = reinterpret_cast<unsigned int*>(fl + 3 * kSPix);          // [kSPix] color() invocations per pixel
-    volatile uint16_t* queue = reinterpret_cast<volatile uint16_t*>(prays + kSPix);  // [C_QUEUES][kQCap]
-    SortedCtl* ctl = reinterpret_cast<SortedCtl*>(const_cast<uint16_t*>(queue) + C_QUEUES * kQCap);
-    volatile unsigned int* vhead = ctl->head;
-    volatile unsigned int* vtail = ctl->tail;
-
-    const int tid = threadIdx.x, lane = tid & 31;
-    const int tiles_x = (rp.nx + kSTile - 1) / kSTile;
-    const int x0 = (blockIdx.x % tiles_x) * kSTile, y0 = (blockIdx.x / tiles_x) * kSTile;
-    const int w_in = min(kSTile, rp.nx - x0), h_in = min(kSTile, rp.ny - y0);
-    const int n_pix = w_in * h_in;  // > 0 for every launched block
-    const bool full_tile = n_pix == kSPix;
-    const uint32_t total = (uint32_t)n_pix * (uint32_t)rp.spp_count;  // < 2^31 (host check: spp_count <= 2^23)
-
-    // pixel slot -> pixel: full tiles use an 8x4-blocked order so that 32 consecutive items are a compact tile
-    auto slot_pixel = [&](uint32_t sl, int& pi, int& pj) {
-        if (full_tile) {
-            pi = x0 + (int)((sl & 7u) | ((sl >> 2) & 8u));
-            pj = y0 + (int)(((sl >> 3) & 3u) | ((sl >> 4) & 12u));
-        } else {
-            const int row = (int)sl / w_in;
-            pj = y0 + row, pi = x0 + (int)sl - row * w_in;
-        }
-    };
-
-    for (int k = tid; k < 3 * kSPix; k += BS) fxlo[k] = 0u, fxhi[k] = 0u, fl[k] = 0.0f;
-    for (int k = tid; k < kSPix; k += BS) prays[k] = 0u;
-    for (int k = tid; k < C_QUEUES * kQCap; k += BS) queue[k] = kQEmpty;
-    __syncthreads();
-    for (int s = tid; s < kSPool; s += BS) queue[C_REGEN * kQCap + s] = (uint16_t)s;  // every slot needs a camera ray
-    if (tid < 8) ctl->head[tid] = 0, ctl->tail[tid] = (tid == C_REGEN) ? kSPool : 0;
-    if (tid == 8) ctl->item_next = 0, ctl->live = kSPool;
-    __syncthreads();
-
-    Rng rng;
-    rng.rk = rp.rk;
-    const int pref = (tid >> 5) % C_TERM;  // the class this warp looks at first: one of the four scatter classes
-    for (;;) {
-        // ---- claim a unit: 32 entries of a class that has them (each warp starts looking at a different class, which
-        // spreads the CAS traffic), else - after a short wait for the warps that are mid-unit - the longest partial run.
-        // Lanes 0..5 each look at one queue.
-        int c = -1, n = 0;
-        unsigned int h = 0;
-        for (int spins = 0;;) {
-            unsigned int hk = 0;
-            int avail = 0;
-            if (lane < C_QUEUES) hk = vhead[lane], avail = (int)(vtail[lane] - hk);
-            const unsigned full = __ballot_sync(0xffffffffu, avail >= 32);
-            int k;
-            if (full) {
-                const unsigned from_pref = full & ~((1u << pref) - 1u);
-                k = __ffs(from_pref ? from_pref : full) - 1;
-                n = 32;
-            } else {
-                const unsigned best = __reduce_max_sync(0xffffffffu, (unsigned)(max(avail, 0) << 3) | (unsigned)(lane & 7));
-                if ((best >> 3) == 0) {  // nothing queued anywhere
-                    if (*(volatile int*)&ctl->live <= 0) break;
-                    __nanosleep(200);
-                    continue;
-                }
-                if (spins < 2) {
-                    spins++;
-                    __nanosleep(300);
-                    continue;
-                }
-                k = (int)(best & 7u), n = (int)(best >> 3);
-            }
-            h = __shfl_sync(0xffffffffu, hk, k);
-            int ok = 0;
-            if (lane == 0) ok = atomicCAS(&ctl->head[k], h, h + (unsigned int)n) == h;
-            if (__shfl_sync(0xffffffffu, ok, 0)) {
-                c = k;
-                break;
-            }
-        }
-        if (c < 0) break;
-        const bool valid = lane < n;
-        const unsigned vmask = __ballot_sync(0xffffffffu, valid);
-#ifdef RTW_SORTED_STATS
-        if (lane == 0 && blockIdx.x == 1000) atomicAdd(&g_stats[c][0], 1), atomicAdd(&g_stats[c][1], n);
-#endif
-        int slot = 0;
-        Ray ray;
-        ray.o = ray.d = mk(0.0f, 0.0f, 0.0f);
-        ray.time = 0.0f;
-        V3 beta = mk(1.0f, 1.0f, 1.0f);
-        uint32_t pix = 0, bounce = 0;
-        bool alive = false;
-        if (valid) {
-            volatile uint16_t* e = queue + c * kQCap + ((h + lane) & (kQCap - 1));
-            uint16_t sv16;
-            while ((sv16 = *e) == kQEmpty) {}  // reserved by a producer that has not written it yet
-            *e = kQEmpty;
-            slot = sv16;
-            __threadfence_block();  // the entry was published after the slot's state
-            if (c <= C_TERM) {      // warp-uniform
-                const float4 a = stA[slot], b = stB[slot], cc = stC[slot];
-                const uint4 d = stD[slot];
-                ray.o = mk(a.x, a.y, a.z), ray.d = mk(b.x, b.y, b.z), ray.time = b.w;
-                beta = mk(cc.x, cc.y, cc.z);
-                HitId hit;
-                hit.t = a.w, hit.prim = fi(cc.w), hit.item = (int)d.x;
-                rng.pixel = d.y, rng.sample = d.z;
-                bounce = d.w & 0xffffu, pix = d.w >> 16;
-                V3 L = mk(0.0f, 0.0f, 0.0f);
-                alive = shade_hit<F, SM>(sc, sv, rng, bounce, hit, ray, beta, L, c == C_LAMB || c == C_DIEL);
-                if (alive && (int)bounce >= rp.max_depth) alive = false;  // :47-48: the next color() returns 0
-                if (!alive) {                                             // :235-239
-                    // the path's color() invocations = its last bounce index; counted per pixel at the path's end (a per-lane
-                    // counter live across the whole loop was the one value this kernel spilled to local memory)
-                    atomicAdd(prays + pix, bounce);
-                    const float v[3] = {L.x, L.y, L.z};
-#pragma unroll
-                    for (int ch = 0; ch < 3; ch++) {
-                        if (v[ch] != 0.0f) {
-                            // below 8192 a pixel's 2^23 samples cannot overflow the 64-bit sum; fireflies up to 2^30 take the
-                            // same (exact, commutative) integer path — it would take > 448 of them at 1e9 in ONE pixel of one
-                            // launch to wrap; only samples >= 2^30 or not finite go to the float side sum
-                            if (fabsf(v[ch]) < 1073741824.0f) {
-                                // two native 32-bit ATOMS.ADD instead of a 64-bit CAS loop: the carry out of the low word (and a
-                                // sample >= 256) goes to the high word; integer adds commute, so the sum stays exact and order-free
-                                const long long fx = __float2ll_rn(v[ch] * 16777216.0f);
-                                const unsigned int lo = (unsigned int)fx;
-                                unsigned int hi = (unsigned int)((unsigned long long)fx >> 32);
-                                const unsigned int old = atomicAdd(fxlo + ch * kSPix + pix, lo);
-                                hi += (old + lo < old) ? 1u : 0u;
-                                if (hi) atomicAdd(fxhi + ch * kSPix + pix, hi);
-                            } else {
-                                atomicAdd(fl + ch * kSPix + pix, v[ch]);
-                            }
-                        }
-                    }
-                }
-            }
-        }
-        __syncwarp();       // reconverge the lanes that added radiance with those that did not
-        if (c >= C_TERM) {  // warp-uniform: every valid lane needs a new path
-            unsigned int item = 0;
-            if (lane == 0) item = atomicAdd(&ctl->item_next, (unsigned int)n);
-            item = __shfl_sync(0xffffffffu, item, 0) + lane;
-            if (valid && item < total) {
-                uint32_t sm;
-                if (full_tile) sm = item >> 8, pix = item & 255u;
-                else sm = item / (uint32_t)n_pix, pix = item - sm * (uint32_t)n_pix;
-                int pi, pj;
-                slot_pixel(pix, pi, pj);
-                rng.pixel = (uint32_t)(pj * rp.nx + pi);
-                rng.sample = (uint32_t)rp.spp_begin + sm;  // global sample index: shards are disjoint streams
-                if (rp.flags & RTW_FLAG_DEBUG_RAY) pi = rp.nx / 2, pj = rp.ny / 2;  // RayTracingWeekend.cpp:221-225
-                ray = camera_ray(sc, rp, rng, pi, pj);
-                beta = mk(1.0f, 1.0f, 1.0f);
-                bounce = 0;
-                alive = true;
-            }
-        }
-        __syncwarp();
-        int ncls = (c >= C_TERM) ? C_DEAD : C_REGEN;  // a terminal/regen lane only stays dead when the pool is empty
-        if (alive) {
-            bounce++;
-            const HitId hit = closest_hit<F, SM, false>(sc, sv, ray.o, ray.d, ray.time, 0.001f, FLT_MAX, &rng, bounce, stack, BS);
-            ncls = C_TERM;
-            if (hit.prim != -1 && sc.render_type != RTW_RENDER_NORMAL) {
-                uint32_t pm;
-                const int mat_idx = hit_material<SM>(sc, sv, hit, pm);
-                const int mt = ld_mat<SM>(sv, sc.off[SEC_MATS] + (uint32_t)mat_idx * 32u).type;
-                // class of material type `mt` from a packed table (one shift instead of a jump table with four divergent
-                // arms): nibble mt of kClassOfMat; any other value shades as lambertian, like the switch in shade_hit
-                constexpr uint32_t kClassOfMat = (uint32_t)C_LAMB << (4 * RTW_MAT_LAMBERTIAN) | (uint32_t)C_METAL << (4 * RTW_MAT_METAL) |
-                                                 (uint32_t)C_DIEL << (4 * RTW_MAT_DIELECTRIC) | (uint32_t)C_TERM << (4 * RTW_MAT_DIFFUSE_LIGHT) |
-                                                 (uint32_t)C_ISO << (4 * RTW_MAT_ISOTROPIC);
-                static_assert(C_LAMB == 0, "nibbles of unknown material types must read as lambertian");
-                ncls = (int)((kClassOfMat >> (min((uint32_t)mt, 7u) * 4u)) & 7u);
-            }
-            stA[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, hit.t);
-            stB[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, ray.time);
-            stC[slot] = make_float4(beta.x, beta.y, beta.z, __int_as_float(hit.prim));
-            stD[slot] = make_uint4((uint32_t)hit.item, rng.pixel, rng.sample, bounce | (pix << 16));
-            __threadfence_block();  // state before the queue entry
-        }
-        if (valid) {
-            const unsigned same = __match_any_sync(vmask, ncls);
-            const int leader = __ffs(same) - 1;
-            unsigned int pos = 0;
-            if (lane == leader) {
-                if (ncls != C_DEAD) pos = atomicAdd(&ctl->tail[ncls], (unsigned int)__popc(same));
-                else atomicSub(&ctl->live, __popc(same));
-            }
-            pos = __shfl_sync(vmask, pos, leader);
-            if (ncls != C_DEAD) {
-                volatile uint16_t* q = queue + ncls * kQCap + ((pos + __popc(same & ((1u << lane) - 1u))) & (kQCap - 1));
-                while (*q != kQEmpty) {}  // claimed one lap ago by a consumer that has not read it yet (header comment)
-                *q = (uint16_t)slot;
-            }
-        }
-    }
-    __syncthreads();
-#ifdef RTW_SORTED_STATS
-    if (tid == 0 && blockIdx.x == 1000)
-        for (int k = 0; k < C_QUEUES; k++) printf("class %d: units %d lanes %d\n", k, g_stats[k][0], g_stats[k][1]);
-#endif
-
-    // one 16-byte store per pixel (canvas[j*nx+i], RayTracingWeekend.cpp:247)
-    for (int p = tid; p < n_pix; p += BS) {
-        int pi, pj;
-        slot_pixel((uint32_t)p, pi, pj);
-        const size_t idx = (size_t)pj * rp.nx + pi;
-        float4 out;
-        out.x = (float)((double)(long long)(((unsigned long long)fxhi[p] << 32) | fxlo[p]) * (1.0 / 16777216.0)) + fl[p];
-        out.y = (float)((double)(long long)(((unsigned long long)fxhi[kSPix + p] << 32) | fxlo[kSPix + p]) * (1.0 / 16777216.0)) + fl[kSPix + p];
-        out.z = (float)((double)(long long)(((unsigned long long)fxhi[2 * kSPix + p] << 32) | fxlo[2 * kSPix + p]) * (1.0 / 16777216.0)) + fl[2 * kSPix + p];
-        out.w = (float)rp.spp_count;
-        if (rp.flags & RTW_FLAG_ACCUMULATE) {
-            const float4 prev = accum[idx];
-            out.x += prev.x, out.y += prev.y, out.z += prev.z, out.w += prev.w;
-        }
-        accum[idx] = out;
-    }
-    unsigned long long warp_rays = 0;
-    for (int p = tid; p < kSPix; p += BS) warp_rays += prays[p];
-    for (int o = 16; o > 0; o >>= 1) warp_rays += __shfl_down_sync(0xffffffffu, warp_rays, o);
-    if (lane == 0 && warp_rays) atomicAdd(ray_counter, warp_rays);
-}
-
-namespace {
-template <uint32_t F, int SM>
-cudaError_t launch_sorted_t(const DevScene& sc, const DevRenderParams& rp, float4* accum, unsigned long long* counter,
-                            size_t smem, cudaStream_t st) {
-    // threads per block, pool slots per 256 threads, resident blocks per SM — one measured triple per variant class (header
-    // comment), written BS * 1000 + PT * 10 + MB so that -DRTW_CFG_x=... can override a class for A/B builds (tools/ab_libs.sh;
-    // nvcc splits -D values at commas)
-#ifndef RTW_CFG_CORNELL
-#define RTW_CFG_CORNELL 512042
-#endif
-#ifndef RTW_CFG_TEX
-#define RTW_CFG_TEX 768061
-#endif
-#ifndef RTW_CFG_BVH_UNSTAGED
-#define RTW_CFG_BVH_UNSTAGED 256022
-#endif
-#ifndef RTW_CFG_BVH_STAGED
-#define RTW_CFG_BVH_STAGED 256023
-#endif
-    constexpr int cfg = (F == kVariants[0]) ? RTW_CFG_CORNELL : ((F & F_BVH) ? (SM < 2 ? RTW_CFG_BVH_UNSTAGED : RTW_CFG_BVH_STAGED) : RTW_CFG_TEX);
-    constexpr int BS = cfg / 1000, PT = cfg / 10 % 100, MB = cfg % 10;
-    static_assert(BS % 32 == 0 && BS <= 1024 && pool_slots(PT) <= 2048, "block size / pool out of range");
-    // `smem` (staged bytes + traversal stacks) was planned for kSBlock threads: the stacks scale with the block size
-    const size_t staged = SM == 2 ? sc.all_bytes : (SM == 1 ? sc.hot_bytes : 0);
-    smem = staged + (smem - staged) / kSBlock * BS;
-    const int tiles_x = (rp.nx + kSTile - 1) / kSTile, tiles_y = (rp.ny + kSTile - 1) / kSTile;
-    const uint32_t pool_off = (uint32_t)((smem + 15) & ~(size_t)15);
-    const size_t bytes = pool_off + sorted_pool_bytes(PT);
-    cudaError_t e = cudaFuncSetAttribute(render_sorted<F, SM, PT, MB, BS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
-    if (e != cudaSuccess) return e;
-    static const bool debug = getenv("RTW_DEBUG_TREES") != nullptr;  // read once per process
-    if (debug) {
-        int nb = 0;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, render_sorted<F, SM, PT, MB, BS>, BS, bytes);
-        fprintf(stderr, "rtw render_sorted<%u,%d,%d,%d,%d>: %zu bytes of shared memory per block (stack %zu), %d blocks/SM\n", F, SM, PT, MB, BS,
-                bytes, smem - staged, nb);
-    }
-    render_sorted<F, SM, PT, MB, BS><<<tiles_x * tiles_y, BS, bytes, st>>>(sc, rp, accum, counter, pool_off);
-    return cudaGetLastError();
-}
-}  // namespace
 
 #ifdef RTW_COUNT_EVENTS
 // diagnostics build: read and clear the traversal event counters of the render kernel (tools/count_tree_events.py)
@@ -372,14 +22,30 @@ extern "C" int rtw_debug_events(unsigned long long* out, int n, int clear) {
 }
 #endif
 
-// spp * max_depth < 2^32: the per-pixel count of color() invocations is 32 bits
-bool sorted_supports(const DevRenderParams& rp) {
-    return rp.spp_count <= (1 << 23) && rp.max_depth < (1 << 16) && (unsigned long long)rp.spp_count * (unsigned long long)rp.max_depth < (1ull << 32);
-}
+// The all-features variants on unstaged scenes (Book-2 final scene) are bound by the SM instruction cache: they
+// are instantiated in sorted_big.cu, which compiles the same template in compact mode (RTW_COMPACT: one out-of-line copy of the
+// Philox rounds instead of one per draw site — +6 % there, -9...-15 % on the variants that fit the cache, which stay here).
+cudaError_t launch_render_sorted_big(const DevScene& sc, const DevRenderParams& rp, float4* accum, unsigned long long* counter, int stage,
+                                     size_t smem, cudaStream_t st);
 
 cudaError_t launch_render_sorted(const DevScene& sc, const DevRenderParams& rp, float4* accum, unsigned long long* counter,
                                  cudaStream_t st) {
-    RTW_DISPATCH(kSBlock, launch_sorted_t, sc, rp, accum, counter);
+#ifdef RTW_COUNT_EVENTS
+    RTW_DISPATCH(kSBlock, launch_sorted_t, sc, rp, accum, counter);  // diagnostics build: one translation unit, one set of counters
+#else
+    Launch l = plan(sc, kSBlock);
+    if (l.stage == 2) {
+        if (l.variant == kVariants[0]) return launch_sorted_t<kVariants[0], 2>(sc, rp, accum, counter, l.smem, st);
+        if (l.variant == kVariants[1]) return launch_sorted_t<kVariants[1], 2>(sc, rp, accum, counter, l.smem, st);
+        if (l.variant == kVariants[2]) return launch_sorted_t<kVariants[2], 2>(sc, rp, accum, counter, l.smem, st);
+        return launch_sorted_t<F_ALL, 2>(sc, rp, accum, counter, l.smem, st);
+    }
+    if (l.variant == kVariants[1]) {
+        if (l.stage == 1) return launch_sorted_t<kVariants[1], 1>(sc, rp, accum, counter, l.smem, st);
+        return launch_sorted_t<kVariants[1], 0>(sc, rp, accum, counter, l.smem, st);
+    }
+    return launch_render_sorted_big(sc, rp, accum, counter, l.stage, l.smem, st);
+#endif
 }
 
 }  // namespace rtw
