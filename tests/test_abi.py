@@ -98,3 +98,33 @@ def test_tonemap_and_ppm_writer(tmp_path):
     assert lines[3 + 2] == f"{int(np.float64(np.float32(255.99)) * c[1, 2, 0])} 0 255"
     assert lines[3 + 3] == "127 255 255"
     assert len([l for l in lines if l]) == 3 + 6
+
+
+def test_multi_gpu_entry_points_argument_handling():
+    """rtw_comm_* / rtw_shard_range / rtw_reduce_accumulators without a GPU: ids, ranges, no-op cases and refusals."""
+    import ctypes as C
+
+    lib = _lib.load()
+    b, n = C.c_int(), C.c_int()
+    for spp, world in ((1024, 8), (100, 8), (5, 3), (0, 2), (7, 16)):
+        got = []
+        for r in range(world):
+            assert lib.rtw_shard_range(spp, r, world, C.byref(b), C.byref(n)) == _lib.RTW_OK
+            got.append((b.value, n.value))
+        assert got[0][0] == 0 and sum(c for _, c in got) == spp
+        assert all(b0 + c0 == b1 for (b0, c0), (b1, _) in zip(got, got[1:]))
+    assert lib.rtw_shard_range(8, 2, 2, C.byref(b), C.byref(n)) != _lib.RTW_OK  # rank out of range
+    assert lib.rtw_shard_range(8, 0, 0, C.byref(b), C.byref(n)) != _lib.RTW_OK
+    # a single rank (or no communicator at all) reduces to a no-op; NULL handles are harmless
+    assert lib.rtw_reduce_accumulators(None, None, 4, 4, 0, None) == _lib.RTW_OK
+    assert lib.rtw_comm_rank(None) == 0 and lib.rtw_comm_world(None) == 1
+    lib.rtw_comm_destroy(None)
+    assert not lib.rtw_comm_create(None, 0, 1, 0)       # no id
+    assert not lib.rtw_comm_adopt(None, 0, 2, 0)        # no communicator
+    ident = (C.c_uint8 * _lib.RTW_COMM_ID_BYTES)()
+    if lib.rtw_comm_unique_id(ident) == _lib.RTW_OK:    # libnccl present: two draws differ
+        other = (C.c_uint8 * _lib.RTW_COMM_ID_BYTES)()
+        assert lib.rtw_comm_unique_id(other) == _lib.RTW_OK and bytes(ident) != bytes(other)
+        assert not lib.rtw_comm_create(ident, 3, 2, 0)  # rank >= world
+    else:
+        assert b"nccl" in lib.rtw_last_error().lower()
