@@ -28,7 +28,7 @@ namespace rtw {
 enum : uint32_t {
     PM_TYPE_MASK = 0x7u,
     PM_FLIP = 1u << 3,
-    PM_PRECISE = 1u << 4,  // sphere with |radius| >= 100: quadratic evaluated in FP64 (ground / fog spheres)
+    PM_PRECISE = 1u << 4,  // sphere with |radius| >= 100 (api.cu precise_min_radius): quadratic evaluated in FP64 (ground / fog spheres)
     PM_XF_SHIFT = 5,
     PM_XF_MASK = 0xFFFu,
     PM_MAT_SHIFT = 17
