@@ -308,6 +308,8 @@ RTW_UNIFIED_FN HitId bvh_hit_items(uint32_t items0, SceneView sv, RayK rk, float
 // with tmax == closest the node boxes are re-tested against the final t, which can change which of several
 // primitives at exactly that t is reported (coplanar faces of adjacent boxes, seen from inside a box).  Rays of a
 // render never start inside closed boxes, so the megakernel skips it; intersect_batch (parity tier 1) runs it.
+// which variants walk all tree items of the world in one loop (kUnified in closest_hit)
+__host__ __device__ constexpr bool unified_variant(uint32_t f, int sm) { return RTW_UNIFIED_BVH && (f & F_BVH) != 0 && !bvh4_variant(f) && sm < 2; }
 template <uint32_t F, int SM, bool EXACT_TIES>
 RTW_DEV HitId closest_hit(const DevScene& sc, const SceneView& sv, V3 o, V3 d, float time, float tmin, float tmax,
                           const Rng* rng, uint32_t bounce, int* stack, int stride) {

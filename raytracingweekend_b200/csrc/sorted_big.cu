@@ -7,6 +7,7 @@
 #ifndef RTW_COUNT_EVENTS
 #define RTW_COMPACT 1
 #define RTW_PHILOX_OOL 1
+#define RTW_PHASED 1
 #include "sorted_kernel.cuh"
 
 namespace rtw {

@@ -18,6 +18,10 @@ sc = r.Scene.named(name, nx / ny)
 tag = " [wavefront]" if flags & 1 else ""
 for _ in range(reps):
     acc, st = sc.render(nx, ny, spp, flags=flags)
+    if os.environ.get("RTW_PROF_HASH") == "2":  # every repetition
+        import hashlib
+
+        print(f"sha256(accum)={hashlib.sha256(acc.tobytes()).hexdigest()[:16]} rays={st['rays']}", flush=True)
     print(f"{name}{tag} {nx}x{ny}x{spp}: launches={st['kernel_launches']} kernel_ms={st['kernel_ms']:.2f} Gpaths/s={st['paths'] / st['kernel_ms'] / 1e6:.3f} "
           f"Grays/s={st['rays'] / st['kernel_ms'] / 1e6:.3f}", flush=True)
 if os.environ.get("RTW_PROF_HASH"):  # A/B of kernels that must give bit-identical images
