@@ -34,6 +34,13 @@ cudaError_t launch_render_sorted(const DevScene& sc, const DevRenderParams& rp, 
     RTW_DISPATCH(kSBlock, launch_sorted_t, sc, rp, accum, counter);  // diagnostics build: one translation unit, one set of counters
 #else
     Launch l = plan(sc, kSBlock);
+    // Staged scenes with media but without trees, textures, moving or huge spheres (Cornell smoke, hittable.h:430-479 over box
+    // boundaries): a variant of their own, for this kernel only.  The all-features kernel they would otherwise run touches far
+    // more code than the SM instruction cache holds (76.9 % hit rate).
+    constexpr uint32_t kSmoke = F_XF | F_MEDIA;
+    static const bool smoke_variant = [] { const char* v = getenv("RTW_SMOKE_VARIANT"); return !v || atoi(v) != 0; }();  // =0: A/B
+    if (smoke_variant && l.stage == 2 && (sc.features & F_MEDIA) && (sc.features & ~kSmoke) == 0)
+        return launch_sorted_t<kSmoke, 2>(sc, rp, accum, counter, sc.all_bytes, st);
     if (l.stage == 2) {
         if (l.variant == kVariants[0]) return launch_sorted_t<kVariants[0], 2>(sc, rp, accum, counter, l.smem, st);
         if (l.variant == kVariants[1]) return launch_sorted_t<kVariants[1], 2>(sc, rp, accum, counter, l.smem, st);

@@ -504,7 +504,10 @@ cudaError_t launch_sorted_t(const DevScene& sc, const DevRenderParams& rp, float
 #ifndef RTW_CFG_BVH_STAGED
 #define RTW_CFG_BVH_STAGED 256023
 #endif
-    constexpr int cfg = (F == kVariants[0]) ? RTW_CFG_CORNELL : ((F & F_BVH) ? (SM < 2 ? RTW_CFG_BVH_UNSTAGED : RTW_CFG_BVH_STAGED) : RTW_CFG_TEX);
+#ifndef RTW_CFG_SMOKE
+#define RTW_CFG_SMOKE RTW_CFG_CORNELL
+#endif
+    constexpr int cfg = (F == kVariants[0]) ? RTW_CFG_CORNELL : (F == (F_XF | F_MEDIA)) ? RTW_CFG_SMOKE : ((F & F_BVH) ? (SM < 2 ? RTW_CFG_BVH_UNSTAGED : RTW_CFG_BVH_STAGED) : RTW_CFG_TEX);
     constexpr int BS = cfg / 1000, PT = cfg / 10 % 100, MB = cfg % 10;
     static_assert(BS % 32 == 0 && BS <= 1024 && pool_slots(PT) <= 2048, "block size / pool out of range");
     // `smem` (staged bytes + traversal stacks) was planned for kSBlock threads: the stacks scale with the block size
