@@ -67,15 +67,20 @@ def build(force: bool = False, verbose: bool = False, extra: list[str] | None = 
     if force or _stale(host_so, host_objs):
         _run(["g++", "-shared", "-o", host_so, *host_objs])
     nvcc = _nvcc()
-    cuda_objs = []
+    cuda_objs, cmds = [], []
     for s in CUDA_SRCS:
         src, obj = os.path.join(CSRC, s), os.path.join(OBJ, s + tag + ".o")
         if force or _stale(obj, [src] + hdrs):
             cmd = [nvcc, *NVCC_ARCH, "-O3", "-lineinfo", "-std=c++17", *NVCC_MATH, *(extra or []), "-Xcompiler", "-fPIC", "-c", src, "-o", obj]
             if verbose:
                 cmd.insert(1, "-Xptxas=-v")
-            _run(cmd)
+            cmds.append(cmd)
         cuda_objs.append(obj)
+    if cmds:  # the translation units are independent: compile them side by side (the kernels' TUs take a minute each)
+        from concurrent.futures import ThreadPoolExecutor
+
+        with ThreadPoolExecutor(max_workers=min(len(cmds), os.cpu_count() or 1)) as pool:
+            list(pool.map(_run, cmds))
     full_so = os.path.join(LIB, f"librtw_b200{tag}.so")
     if force or _stale(full_so, host_objs + cuda_objs):
         _run([nvcc, *NVCC_ARCH, "-shared", "-o", full_so, *host_objs, *cuda_objs, "-cudart", "static"])
