@@ -430,7 +430,9 @@ def bench_config(ctx: Ctx, cfg_name: str, steps: int, warmup: int, with_cpu: boo
                 # opcode): ncu sm__inst_issued / issue slots of the committed capture; the algorithmic count above excludes
                 # compares, selects, address/loop arithmetic and the Philox integer rounds
                 "issue_slots_busy_ncu": ncu.get("issue_slots_busy") if sorted_kernel else None,
-                "kernel": "render_sorted (material-sorted megakernel, csrc/sorted.cu)" if sorted_kernel else "render_megakernel",
+                "kernel": (("render_sorted, phased form (shade units / closest_hit units alternate per block: the code outgrows the SM "
+                            "instruction cache; csrc/sorted_kernel.cuh, sorted_big.cu)") if cfg_name == "cfg3" and os.environ.get("RTW_PHASED", "1") != "0"
+                           else "render_sorted (material-sorted megakernel, csrc/sorted_kernel.cuh)") if sorted_kernel else "render_megakernel",
                 "kernel_ms_per_launch": kern_ms / max(1, total_launches // world),
                 "hbm": {"algorithmic_bytes_per_launch": NX * NY * 16, "achieved_gbs": NX * NY * 16 / (kern_ms / steps * 1e-3) / 1e9,
                         "peak_gbs": peaks.get("hbm_gbs"), "note": "not HBM-bound: one 16-byte store per pixel per launch"}}
