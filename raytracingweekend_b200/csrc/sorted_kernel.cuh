@@ -15,7 +15,7 @@
 //            lanes) -> classify -> store state -> push.  Terminal units add their radiance and start 32 new camera
 //            rays on the spot, so camera maths also runs at full lanes.
 //
-// Rings: capacity >= number of slots, 16-bit entries = slot id | lap bit.  A consumer takes (and clears) its entries right after
+// Rings: capacity >= number of slots, 16-bit entries = slot id | lap of the ring index (4 bits).  A consumer takes (and clears) its entries right after
 // the CAS that claimed them, waiting for an entry of ITS lap where the producer has not written yet; a producer waits until its
 // target position is empty before it writes, so a delayed consumer is never overwritten (ring_take / ring_put below).
 // Per-pixel sums are 64-bit fixed point (2^-24) in shared memory (kept as two 32-bit words, see the adds): integer adds commute, so the image stays
@@ -91,12 +91,12 @@ __device__ int g_stats[8][2];
 //    (`while (*e == kQEmpty) {}  *e = kQEmpty;`) the store lands behind the loop's reconvergence point (BSYNC, then STS): a lane
 //    that has its entry clears its position only when the slowest lane of its warp has one too, and a lane whose position is
 //    free writes only when all are — "claimed but not cleared" then lasts as long as the slowest producer, not a few cycles;
-//  * entries carry the LAP of their ring index in bit 15 ((index / capacity) & 1), and a consumer only accepts an entry of its
-//    own lap.  Seen without it (256 threads x 512 slots, capacity 512: 3 of 11 renders wrong, then 3 of 41 with the PTX loops,
-//    0 of 41 with the lap bit): a producer held up between its reservation and its write while the ring went round once; the
+//  * entries carry the LAP of their ring index in bits 12-15 ((index / capacity) & 15; slot ids are < 2^11, so no entry equals
+//    the empty mark 0xffff), and a consumer only accepts an entry of its own lap.  Seen without it (256 threads x 512 slots, capacity 512: 3 of 11 renders wrong, then 3 of 41 with the PTX loops,
+//    0 of 41 with one lap bit, which the four replaced): a producer held up between its reservation and its write while the ring went round once; the
 //    consumers of index i and of index i + capacity both spin on the position and both take the entry the moment it lands —
-//    one slot owned twice, another orphaned for a lap.  With the lap bit it takes a hold-up of TWO laps.
-// ring_take: wait until the position holds an entry of lap `tag` (0 or 0x8000), take it and leave the position empty.
+//    one slot owned twice, another orphaned for a lap.  With four lap bits it takes a hold-up of SIXTEEN laps.
+// ring_take: wait until the position holds an entry of lap `tag` (lap << 12), take it and leave the position empty.
 __device__ __forceinline__ int ring_take(uint32_t saddr, uint32_t tag) {
     uint32_t v;
     asm volatile(
@@ -108,19 +108,19 @@ __device__ __forceinline__ int ring_take(uint32_t saddr, uint32_t tag) {
         "RTW_RING_TAKE:\n\t"
         "ld.volatile.shared.u16 t, [%1];\n\t"
         "cvt.u32.u16 w, t;\n\t"
-        "and.b32 x, w, 0x8000;\n\t"
+        "and.b32 x, w, 0xf000;\n\t"
         "setp.eq.u32 p, x, %2;\n\t"
         "setp.ne.and.u32 p, w, 0xffff, p;\n\t"
         "@p st.volatile.shared.u16 [%1], e;\n\t"
         "@!p bra RTW_RING_TAKE;\n\t"
-        "and.b32 %0, w, 0x7fff;\n\t"
+        "and.b32 %0, w, 0x0fff;\n\t"
         "}"
         : "=r"(v)
         : "r"(saddr), "r"(tag)
         : "memory");
     return (int)v;
 }
-// ring_put: wait until the position is empty (its consumer of one lap ago has read it), then write the entry (slot | lap bit).
+// ring_put: wait until the position is empty (its consumer of one lap ago has read it), then write the entry (slot | lap << 12).
 __device__ __forceinline__ void ring_put(uint32_t saddr, uint16_t entry) {
     asm volatile(
         "{\n\t"
@@ -225,7 +225,7 @@ __global__ void __launch_bounds__(BS, MB) render_sorted(const __grid_constant__ 
     // entry `pos` of class ring `cls`, claimed by this warp: wait for its producer, take it, leave the position empty
     auto take = [&](int cls, unsigned int pos) -> int {
         const int v = ring_take((uint32_t)__cvta_generic_to_shared(const_cast<uint16_t*>(queue + cls * kQCap + (pos & (kQCap - 1)))),
-                                (pos & (unsigned int)kQCap) ? 0x8000u : 0u);
+                                ((pos / (unsigned int)kQCap) & 15u) << 12);
 #ifdef RTW_SORTED_CHECK
         {
             const int prev = atomicExch(&own[v], 1 + (tid >> 5));
@@ -262,7 +262,7 @@ __global__ void __launch_bounds__(BS, MB) render_sorted(const __grid_constant__ 
         if (ncls != C_DEAD) {
             const unsigned int idx = pos + (unsigned int)__popc(same & ((1u << lane) - 1u));
             ring_put((uint32_t)__cvta_generic_to_shared(const_cast<uint16_t*>(queue + ncls * kQCap + (idx & (kQCap - 1)))),
-                     (uint16_t)((unsigned int)slot | ((idx & (unsigned int)kQCap) ? 0x8000u : 0u)));
+                     (uint16_t)((unsigned int)slot | (((idx / (unsigned int)kQCap) & 15u) << 12)));
         }
     };
     // class queue of a hit: the material's class, or terminal for a miss (and for every hit of a normal-render)
@@ -509,7 +509,7 @@ cudaError_t launch_sorted_t(const DevScene& sc, const DevRenderParams& rp, float
 #endif
     constexpr int cfg = (F == kVariants[0]) ? RTW_CFG_CORNELL : (F == (F_XF | F_MEDIA)) ? RTW_CFG_SMOKE : ((F & F_BVH) ? (SM < 2 ? RTW_CFG_BVH_UNSTAGED : RTW_CFG_BVH_STAGED) : RTW_CFG_TEX);
     constexpr int BS = cfg / 1000, PT = cfg / 10 % 100, MB = cfg % 10;
-    static_assert(BS % 32 == 0 && BS <= 1024 && pool_slots(PT) <= 2048, "block size / pool out of range");
+    static_assert(BS % 32 == 0 && BS <= 1024 && pool_slots(PT) <= 2048, "block size / pool out of range (ring entries hold 11-bit slot ids)");
     // `smem` (staged bytes + traversal stacks) was planned for kSBlock threads: the stacks scale with the block size
     const size_t staged = SM == 2 ? sc.all_bytes : (SM == 1 ? sc.hot_bytes : 0);
     const int tiles_x = (rp.nx + kSTile - 1) / kSTile, tiles_y = (rp.ny + kSTile - 1) / kSTile;
