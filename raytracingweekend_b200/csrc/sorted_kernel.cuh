@@ -92,10 +92,11 @@ __device__ int g_stats[8][2];
 //    that has its entry clears its position only when the slowest lane of its warp has one too, and a lane whose position is
 //    free writes only when all are — "claimed but not cleared" then lasts as long as the slowest producer, not a few cycles;
 //  * entries carry the LAP of their ring index in bits 12-15 ((index / capacity) & 15; slot ids are < 2^11, so no entry equals
-//    the empty mark 0xffff), and a consumer only accepts an entry of its own lap.  Seen without it (256 threads x 512 slots, capacity 512: 3 of 11 renders wrong, then 3 of 41 with the PTX loops,
-//    0 of 41 with one lap bit, which the four replaced): a producer held up between its reservation and its write while the ring went round once; the
-//    consumers of index i and of index i + capacity both spin on the position and both take the entry the moment it lands —
-//    one slot owned twice, another orphaned for a lap.  With four lap bits it takes a hold-up of SIXTEEN laps.
+//    the empty mark 0xffff), and a consumer only accepts an entry of its own lap.  Seen without it (256 threads x 512 slots,
+//    capacity 512: 3 of 11 renders wrong, then 3 of 41 with the PTX loops, 0 of 41 with one lap bit, which the four replaced):
+//    a producer held up between its reservation and its write while the ring went round once; the consumers of index i and of
+//    index i + capacity both spin on the position and both take the entry the moment it lands — one slot owned twice,
+//    another orphaned for a lap.  With four lap bits it takes a hold-up of SIXTEEN laps.
 // ring_take: wait until the position holds an entry of lap `tag` (lap << 12), take it and leave the position empty.
 __device__ __forceinline__ int ring_take(uint32_t saddr, uint32_t tag) {
     uint32_t v;
