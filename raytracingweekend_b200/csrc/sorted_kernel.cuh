@@ -537,7 +537,15 @@ cudaError_t launch_sorted_t(const DevScene& sc, const DevRenderParams& rp, float
 #endif
         constexpr int PBS = RTW_CFG_PHASED / 1000, PPT = RTW_CFG_PHASED / 10 % 100, PMB = RTW_CFG_PHASED % 10;
         static const bool phased = [] { const char* v = getenv("RTW_PHASED"); return !v || atoi(v) != 0; }();  // RTW_PHASED=0: the plain kernel (A/B)
-        if (phased) return launch(render_sorted<F, SM, PPT, PMB, PBS, true>, PBS, PPT, PMB, true);
+        // its 512 stack columns and 1024 slots must fit the block's shared memory (deep trees: the plain kernel has half the columns)
+        static const size_t smem_max = [] {
+            int dev = 0, v = 0;
+            cudaGetDevice(&dev);
+            cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+            return (size_t)v;
+        }();
+        const size_t need = ((staged + (smem - staged) / kSBlock * PBS + 15) & ~(size_t)15) + sorted_pool_bytes(PPT, true);
+        if (phased && need <= smem_max) return launch(render_sorted<F, SM, PPT, PMB, PBS, true>, PBS, PPT, PMB, true);
     }
     return launch(render_sorted<F, SM, PT, MB, BS, false>, BS, PT, MB, false);
 }
