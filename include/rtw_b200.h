@@ -304,7 +304,9 @@ typedef struct rtw_render_stats {
  *                    stats->rays/kernel_ms are valid after rtw_render_device_finish.  ONE render in flight per
  *                    rtw_scene (its ray counter and timing events live in the scene): a second rtw_render_device
  *                    before rtw_render_device_finish returns RTW_ERR_INVALID.  With RTW_FLAG_WAVEFRONT the call is
- *                    synchronous (the host polls the pool between chunks of iterations). */
+ *                    synchronous (the host polls the pool between chunks of iterations).
+ *                    rtw_render / rtw_render_device_finish return RTW_ERR_CUDA (and the image must be discarded) if the
+ *                    render kernel's watchdog fired: a block found no work for over a second with paths still in flight. */
 int rtw_render(rtw_scene* s, const rtw_render_params* p, float* accum_host_rgba, rtw_render_stats* stats);
 int rtw_render_device(rtw_scene* s, const rtw_render_params* p, float* accum_dev_rgba, void* cuda_stream);
 int rtw_render_device_finish(rtw_scene* s, rtw_render_stats* stats);

@@ -1078,7 +1078,7 @@ extern "C" rtw_scene* rtw_scene_create(const rtw_flat_scene* fs, int device) {
     rtw_scene* s = new (std::nothrow) rtw_scene();
     if (!s) return nullptr;
     s->device = device;
-    cudaError_t err[] = {s->blob.upload(blob), s->texels.upload(texels), dev_alloc((void**)&s->d_counter, 2 * sizeof(unsigned long long)),  // [0] rays, [1] render_sorted's tile counter
+    cudaError_t err[] = {s->blob.upload(blob), s->texels.upload(texels), dev_alloc((void**)&s->d_counter, 2 * sizeof(unsigned long long)),  // [0] rays, [1] render_sorted's watchdog flag
                          cudaEventCreate(&s->ev0), cudaEventCreate(&s->ev1)};
     for (cudaError_t x : err)
         if (x != cudaSuccess) {
@@ -1223,9 +1223,14 @@ extern "C" int rtw_render_device_finish(rtw_scene* s, rtw_render_stats* stats) {
     if (e != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
     if ((e = cudaEventSynchronize(s->ev1)) != cudaSuccess) return cuda_fail(e, "render kernel");
     s->pending = false;
+    unsigned long long counters[2] = {0, 0};  // [0] color() invocations, [1] set by render_sorted's watchdog (sorted_kernel.cuh)
+    if ((e = cudaMemcpy(counters, s->d_counter, sizeof counters, cudaMemcpyDeviceToHost)) != cudaSuccess) return cuda_fail(e, "counter");
+    if (counters[1] != 0) {
+        set_error("render: a block of the sorted kernel found no work for over a second with paths still in flight and gave up (path slot lost); the image is incomplete");
+        return RTW_ERR_CUDA;
+    }
     if (stats) {
-        unsigned long long rays = 0;
-        if ((e = cudaMemcpy(&rays, s->d_counter, sizeof rays, cudaMemcpyDeviceToHost)) != cudaSuccess) return cuda_fail(e, "counter");
+        const unsigned long long rays = counters[0];
         float ms = 0;
         cudaEventElapsedTime(&ms, s->ev0, s->ev1);
         const rtw_render_params& p = s->pending_params;

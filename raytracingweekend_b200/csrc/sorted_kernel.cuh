@@ -289,6 +289,7 @@ __global__ void __launch_bounds__(BS, MB) render_sorted(const __grid_constant__ 
         // Lanes 0..5 each look at one queue.
         int c = -1, n = 0;
         unsigned int h = 0;
+        int idle_polls = 0;
         for (int spins = 0;;) {
             unsigned int hk = 0;
             int avail = 0;
@@ -312,6 +313,12 @@ __global__ void __launch_bounds__(BS, MB) render_sorted(const __grid_constant__ 
                 const unsigned best = __reduce_max_sync(0xffffffffu, (unsigned)(max(avail, 0) << 3) | (unsigned)(lane & 7));
                 if ((best >> 3) == 0) {  // nothing queued anywhere
                     if (*(volatile int*)&ctl->live <= 0) break;
+                    // watchdog: paths in flight but nothing to do for > 1.6 s (a tile's tail is milliseconds) means a slot was
+                    // lost; leave with an error flag (ray_counter[1], read by rtw_render_device_finish) instead of polling forever
+                    if (++idle_polls > (1 << 23)) {
+                        if (lane == 0) atomicExch(ray_counter + 1, 1ull);
+                        break;
+                    }
                     __nanosleep(200);  // (doubling the wait up to 1.6 or 6.4 us while nothing turns up changes nothing: r2_ab_phased.txt)
                     continue;
                 }
